@@ -1,0 +1,181 @@
+/* bvg.h -- C ABI of libbvg.so: the B200 (sm_100a) BigVGAN-v2 vocoder forward path.
+ *
+ * This is the native-op boundary that replaces the reference's torch extension
+ *   /root/reference/indextts/s2mel/modules/bigvgan/alias_free_activation/cuda/   (BV/AF/cuda below)
+ *       anti_alias_activation.cpp:19-23      pybind `forward(input, up_ftr, down_ftr, alpha, beta)`
+ *       anti_alias_activation_cuda.cu:212-246 `fwd_cuda` (callee-allocated torch::Tensor, current stream)
+ * and the ATen/cuDNN calls the reference makes for the rest of the generator
+ *   /root/reference/indextts/s2mel/modules/bigvgan/bigvgan.py                    (BV/bigvgan.py below)
+ * with a real C interface: plain pointers and sizes, no torch types, no C++ exceptions.
+ *
+ * Conventions
+ *  - every pointer is a DEVICE pointer unless the name ends in _host; the caller owns all memory (inputs,
+ *    outputs, workspace) and keeps it alive until `stream` has been synchronised;
+ *  - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream); the library never
+ *    synchronises, never allocates device memory and keeps no global mutable state: concurrent calls from
+ *    several host threads on different streams are safe (the reference's server does that, serve_tars.py:66);
+ *  - every function returns BVG_OK (0) or a negative bvg_status; the message is available from
+ *    bvg_last_error() (thread-local).  Unsupported device / dtype / shape is an ERROR, never a fallback;
+ *  - 64-bit indexing throughout (the reference kernel overflows int32 at B*C*T >= 2^31, .cu:68-74);
+ *  - layouts: "ncl" = [B, C, T] time innermost (the reference's public layout),
+ *             "nlc" = [B, T, C] channel innermost (the library's internal layout for the implicit-GEMM convs).
+ */
+#ifndef BVG_H_
+#define BVG_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BVG_VERSION 100
+
+#if defined(__GNUC__)
+#define BVG_API __attribute__((visibility("default")))
+#else
+#define BVG_API
+#endif
+
+typedef enum {
+    BVG_OK = 0,
+    BVG_ERR_INVALID = -1,     /* bad argument (null pointer, shape, alignment) */
+    BVG_ERR_UNSUPPORTED = -2, /* dtype / shape / hyper-parameter outside what the kernels implement */
+    BVG_ERR_DEVICE = -3,      /* not an sm_100 device */
+    BVG_ERR_CUDA = -4,        /* a CUDA runtime / driver call failed */
+    BVG_ERR_WORKSPACE = -5    /* workspace too small */
+} bvg_status;
+
+typedef enum { BVG_F32 = 0, BVG_BF16 = 1 } bvg_dtype;
+
+/* bvg_precision: arithmetic mode of the convolutions.
+ *   BVG_EXACT_F32 : fp32 operands, fp32 FMA accumulation (CUDA cores), accurate sin  -> the fp32 parity mode
+ *   BVG_BF16_TC   : bf16 operands on tcgen05 tensor cores with fp32 TMEM accumulation; fp32 residual stream and
+ *                   fp32 Activation1d arithmetic                                     -> the throughput mode   */
+typedef enum { BVG_EXACT_F32 = 0, BVG_BF16_TC = 1 } bvg_precision;
+
+#define BVG_MAX_STAGES 8
+#define BVG_MAX_KERNELS 4
+#define BVG_MAX_DILATIONS 4
+#define BVG_MAX_PHASES 8
+
+/* ---------------------------------------------------------------------------------------------------------- */
+/* diagnostics                                                                                                 */
+BVG_API const char* bvg_last_error(void);
+BVG_API int bvg_version(void);
+/* BVG_OK iff `device` (or the current device when < 0) has compute capability 10.x.  Replaces the reference's
+ * silent torch fallback at infer_v2.py:176-182 with a hard error. */
+BVG_API int bvg_device_check(int device);
+/* number of kernel launches issued by this library on the calling thread since the last reset (bench.py's
+ * gpu_launches claim) */
+BVG_API int64_t bvg_launch_count(void);
+BVG_API void bvg_reset_launch_count(void);
+
+/* ---------------------------------------------------------------------------------------------------------- */
+/* (a) fused anti-aliased activation: y = down2(snake_beta(up2(x)))
+ * Replaces BV/AF/cuda/anti_alias_activation_cuda.cu:43-246 and the torch path BV/AF/torch/act.py:25-30
+ * (resample.py:30-38, activations.py:107-120, filter.py:94-101).  The 12-tap Kaiser-sinc filter
+ * (filter.py:30-62, cutoff 0.25, half-width 0.3) is a compile-time constant.
+ * alpha_log / beta_log: per-channel fp32 parameters in LOG scale (the kernel applies exp, like the reference
+ * extension, activation1d.py:68-72).
+ * precise != 0: range-reduced polynomial sin (fp32 parity mode); 0: MUFU approximations.                     */
+
+/* ncl layout.  x element strides: x[b][c][t] = x[b*x_stride_b + c*x_stride_c + t] (time stride 1; honours the
+ * non-contiguous time slice infer_v2.py:856 produces).  y is dense [B, C, T].  dtype applies to x and y. */
+BVG_API int bvg_activation1d_fwd(const void* x, void* y, const float* alpha_log, const float* beta_log, int64_t B, int64_t C,
+                         int64_t T, int64_t x_stride_b, int64_t x_stride_c, int dtype, int precise, void* stream);
+
+/* nlc layout, dense.  C % 8 == 0.  in/out dtypes independent (fp32 residual stream in, bf16 MMA operand out). */
+BVG_API int bvg_activation1d_nlc_fwd(const void* x, int x_dtype, void* y, int y_dtype, const float* alpha_log,
+                             const float* beta_log, int64_t B, int64_t T, int64_t C, int precise, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------------- */
+/* weight preparation (BV/bigvgan.py:388-400 remove_weight_norm is where the host calls these)                 */
+
+/* w[r, :] = g[r] * v[r, :] / ||v[r, :]||_2  (torch._weight_norm(v, g, dim=0)); rows = dim 0, row_len = rest. */
+BVG_API int bvg_fold_weight_norm(const float* v, const float* g, float* w, int64_t rows, int64_t row_len, void* stream);
+
+/* Conv1d weight [Cout, Cin, k] fp32 -> tap-major K-major [k][Cout][Cin] in `dtype` (bf16 for BVG_BF16_TC). */
+BVG_API int bvg_pack_conv1d_weight(const float* w, void* out, int64_t Cout, int64_t Cin, int64_t k, int dtype, void* stream);
+
+/* ConvTranspose1d weight [Cin, Cout, K] fp32 -> polyphase [K/u][u*Cout][Cin]: row n = r*Cout + co of tap j holds
+ * w[:, co, (r+p)%u + u*(K/u-1-j)], p = (K-u)/2; tap j of phase r reads input row q + floor((r+p)/u)-(K/u-1)+j.
+ * No zero-stuffed tensor is ever formed (north_star (c)).  K % u == 0. */
+BVG_API int bvg_pack_convtranspose1d_weight(const float* w, void* out, int64_t Cin, int64_t Cout, int64_t K, int64_t u,
+                                    int dtype, void* stream);
+
+/* layout changes at the path's edges */
+BVG_API int bvg_ncl_to_nlc(const void* x, int x_dtype, int64_t x_stride_b, int64_t x_stride_c, void* y, int y_dtype, int64_t B,
+                   int64_t C, int64_t T, void* stream);
+BVG_API int bvg_nlc_to_ncl(const void* x, int x_dtype, void* y, int y_dtype, int64_t B, int64_t C, int64_t T, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------------- */
+/* (b) dilated Conv1d as implicit GEMM, nlc layout.  Replaces nn.Conv1d / cuDNN at BV/bigvgan.py:58-66,75-83,
+ * 285-287.
+ *   y[b,t,co] = out_scale * ( sum_{j<k} sum_ci w[j][co][ci] * x[b, t + (j-(k-1)/2)*dilation, ci] + bias[co]
+ *                             + residual[b,t,co] ) + accum[b,t,co]
+ * x: [B,T,Cin] (bf16 for BVG_BF16_TC, fp32 for BVG_EXACT_F32), zero outside [0,T);
+ * w_packed from bvg_pack_conv1d_weight in the matching dtype; bias fp32 or NULL; residual / accum fp32 [B,T,Cout]
+ * or NULL (accum may alias y_f32); outputs: y_f32 and/or y_bf16 (either may be NULL, not both).
+ * Cin % 8 == 0, Cout % 8 == 0, k odd <= 11.                                                                   */
+BVG_API int bvg_conv1d_nlc_fwd(const void* x, const void* w_packed, const float* bias, const float* residual,
+                       const float* accum, float* y_f32, void* y_bf16, int64_t B, int64_t T, int64_t Cin, int64_t Cout,
+                       int k, int dilation, float out_scale, int precision, void* stream);
+
+/* (c) ConvTranspose1d(Cin, Cout, K, stride u, padding (K-u)/2) in polyphase form, nlc layout.  Replaces
+ * nn.ConvTranspose1d at BV/bigvgan.py:305-313.  x: [B,Tin,Cin]; y: [B, u*Tin, Cout].                         */
+BVG_API int bvg_convtranspose1d_nlc_fwd(const void* x, const void* w_packed, const float* bias, float* y_f32, void* y_bf16,
+                                int64_t B, int64_t Tin, int64_t Cin, int64_t Cout, int K, int u, int precision,
+                                void* stream);
+
+/* activation_post output -> conv_post (Cin -> 1, k taps, optional bias) -> clamp(-1,1) or tanh, fp32.
+ * Replaces BV/bigvgan.py:379-384.  x: fp32 nlc [B,T,Cin]; w: fp32 [Cin][k] (the module's [1,Cin,k] weight);
+ * y: fp32 [B,1,T]. */
+BVG_API int bvg_conv_post_fwd(const float* x, const float* w, const float* bias, float* y, int64_t B, int64_t T, int64_t Cin,
+                      int k, int use_tanh, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------------- */
+/* whole generator (BV/bigvgan.py:360-386 BigVGAN.forward)                                                     */
+typedef struct {
+    const void* w;     /* packed weight (bvg_pack_*), dtype per precision */
+    const float* bias; /* [Cout] or NULL */
+    int32_t cin, cout, k, dilation;
+} bvg_conv_desc;
+
+typedef struct {
+    const float* alpha_log; /* [C] */
+    const float* beta_log;  /* [C] */
+} bvg_act_desc;
+
+typedef struct {
+    int32_t num_mels;
+    int32_t upsample_initial_channel;
+    int32_t num_stages;                         /* len(upsample_rates) */
+    int32_t num_kernels;                        /* len(resblock_kernel_sizes) */
+    int32_t num_dilations;                      /* len(resblock_dilation_sizes[j]) */
+    int32_t upsample_rates[BVG_MAX_STAGES];
+    int32_t upsample_kernel_sizes[BVG_MAX_STAGES];
+    int32_t use_tanh_at_final;
+    int32_t precision;                          /* bvg_precision */
+    bvg_conv_desc conv_pre;
+    bvg_conv_desc ups[BVG_MAX_STAGES];          /* k = transposed-conv kernel size K, dilation unused */
+    bvg_conv_desc convs1[BVG_MAX_STAGES][BVG_MAX_KERNELS][BVG_MAX_DILATIONS];
+    bvg_conv_desc convs2[BVG_MAX_STAGES][BVG_MAX_KERNELS][BVG_MAX_DILATIONS];
+    bvg_act_desc acts[BVG_MAX_STAGES][BVG_MAX_KERNELS][2 * BVG_MAX_DILATIONS];
+    bvg_act_desc act_post;
+    bvg_conv_desc conv_post;                    /* w: fp32 [1][Cin][k] as stored by the module */
+} bvg_model_desc;
+
+/* bytes of scratch bvg_forward needs for a [B, num_mels, T_mel] input */
+BVG_API size_t bvg_workspace_bytes(const bvg_model_desc* m_host, int64_t B, int64_t T_mel);
+
+/* mel: fp32 [B, num_mels, T_mel] with element strides (mel_stride_b, mel_stride_c, 1);
+ * wav: fp32 [B, 1, T_mel * prod(upsample_rates)], values in [-1, 1].  m_host is a HOST struct of device pointers. */
+BVG_API int bvg_forward(const bvg_model_desc* m_host, const float* mel, int64_t mel_stride_b, int64_t mel_stride_c, float* wav,
+                int64_t B, int64_t T_mel, void* workspace, size_t workspace_bytes, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BVG_H_ */

@@ -1,0 +1,519 @@
+"""BigVGAN-v2 generator with the reference's Python surface and a B200-native forward.
+
+Mirrors ``indextts/s2mel/modules/bigvgan/bigvgan.py`` of the reference: ``load_hparams_from_json`` (:25-28),
+``AMPBlock1`` (:31-147), ``AMPBlock2`` (:150-240), ``BigVGAN`` (:243-492) -- same constructor arguments, same
+module tree, same 783 / 667 state-dict keys, same RNG consumption during construction (so a seeded construction
+yields the reference's weights bit for bit), ``remove_weight_norm()``, ``from_pretrained`` / ``_save_pretrained``.
+
+What differs is everything below ``forward``: the module tree only *stores* parameters.  ``BigVGAN.forward`` folds
+weight-norm and packs the weights once (tap-major bf16 for the tcgen05 implicit-GEMM kernels, polyphase for the
+transposed convs) and then makes ONE call into ``libbvg.so`` (``bvg_forward``), which launches the whole generator
+on the caller's current CUDA stream.  ``use_cuda_kernel`` is accepted and stored but selects nothing: the sm_100a
+kernels are the only implementation, and a CPU tensor or a non-sm_100 device raises.
+"""
+from __future__ import annotations
+
+import ctypes
+import json
+import os
+import weakref
+from pathlib import Path
+from typing import Dict, Optional, Union
+
+import torch
+import torch.nn as nn
+from torch.nn.utils import remove_weight_norm, weight_norm
+
+try:  # the reference requires huggingface_hub (bigvgan.py:22); keep working without it for local use
+    from huggingface_hub import PyTorchModelHubMixin, hf_hub_download
+except Exception:  # pragma: no cover
+    class PyTorchModelHubMixin:  # type: ignore
+        def __init_subclass__(cls, **kwargs):
+            super().__init_subclass__()
+
+    hf_hub_download = None
+
+from . import _lib, activations, ops
+from .alias_free_activation.torch.act import Activation1d as TorchActivation1d
+from .env import AttrDict
+from .utils import get_padding, init_weights
+
+DEFAULT_PRECISION = os.environ.get("BVG_PRECISION", "bf16")
+
+
+def load_hparams_from_json(path) -> AttrDict:
+    with open(path) as f:
+        data = f.read()
+    return AttrDict(json.loads(data))
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# parameter-holding conv modules whose forward is the libbvg kernel
+# ---------------------------------------------------------------------------------------------------------------
+def _packed_cache(module, key, build):
+    """Cache a derived tensor on ``module`` keyed by the versions of the tensors it was derived from."""
+    cache = module.__dict__.setdefault("_bvg_cache", {})
+    hit = cache.get(key[0])
+    if hit is not None and hit[0] == key:
+        return hit[1]
+    val = build()
+    cache[key[0]] = (key, val)
+    return val
+
+
+def _weight_sources(m):
+    if hasattr(m, "weight_v"):
+        return (m.weight_v, m.weight_g)
+    return (m.weight,)
+
+
+def _effective_weight(m) -> torch.Tensor:
+    """Folded fp32 weight of a (possibly weight-normed) conv module, computed by ``bvg_fold_weight_norm``."""
+    if hasattr(m, "weight_v"):
+        return ops.fold_weight_norm(m.weight_v, m.weight_g)
+    return m.weight.detach().float().contiguous()
+
+
+def _fingerprint(tensors):
+    return tuple((t.data_ptr(), t._version, t.device.index) for t in tensors)
+
+
+class Conv1d(nn.Conv1d):
+    """``nn.Conv1d`` as a parameter container; ``forward`` runs the libbvg implicit-GEMM kernel ([B,C,T] in/out).
+    Only what the generator uses is supported: stride 1, zeros 'same' padding, groups 1."""
+
+    bvg_precision = None
+
+    def packed(self, precision: int) -> torch.Tensor:
+        src = _weight_sources(self)
+        return _packed_cache(self, ("w", precision) + _fingerprint(src),
+                             lambda: ops.pack_conv1d_weight(_effective_weight(self), precision))
+
+    def forward(self, x):
+        k, d = self.kernel_size[0], self.dilation[0]
+        if self.stride[0] != 1 or self.groups != 1 or self.padding[0] != get_padding(k, d) or k % 2 == 0:
+            raise NotImplementedError("libbvg Conv1d: stride 1, groups 1, odd kernel and 'same' zero padding only")
+        prec = ops.precision_code(self.bvg_precision or DEFAULT_PRECISION)
+        if self.out_channels % 8 != 0:  # conv_post (C -> 1): the dedicated tail kernel without the clamp is not exposed
+            raise NotImplementedError("libbvg Conv1d: out_channels must be a multiple of 8 (conv_post is fused into "
+                                      "BigVGAN.forward)")
+        op_dtype = torch.bfloat16 if prec == _lib.BVG_BF16_TC else torch.float32
+        xn = ops.ncl_to_nlc(x.float() if x.dtype not in (torch.float32, torch.bfloat16) else x, op_dtype)
+        bias = None if self.bias is None else self.bias.detach().float().contiguous()
+        y = ops.conv1d_nlc(xn, self.packed(prec), bias, d, prec)
+        return ops.nlc_to_ncl(y, x.dtype if x.dtype in (torch.float32, torch.bfloat16) else torch.float32)
+
+
+class ConvTranspose1d(nn.ConvTranspose1d):
+    """``nn.ConvTranspose1d`` as a parameter container; ``forward`` runs the polyphase libbvg kernel."""
+
+    bvg_precision = None
+
+    def packed(self, precision: int) -> torch.Tensor:
+        src = _weight_sources(self)
+        return _packed_cache(self, ("w", precision) + _fingerprint(src),
+                             lambda: ops.pack_convtranspose1d_weight(_effective_weight(self), self.stride[0], precision))
+
+    def forward(self, x, output_size=None):
+        K, u = self.kernel_size[0], self.stride[0]
+        if self.padding[0] != (K - u) // 2 or K % u != 0 or (K - u) % 2 != 0 or self.groups != 1 or \
+                self.output_padding[0] != 0 or self.dilation[0] != 1:
+            raise NotImplementedError("libbvg ConvTranspose1d: K % stride == 0 and padding (K-stride)/2 only")
+        prec = ops.precision_code(self.bvg_precision or DEFAULT_PRECISION)
+        op_dtype = torch.bfloat16 if prec == _lib.BVG_BF16_TC else torch.float32
+        xn = ops.ncl_to_nlc(x, op_dtype)
+        bias = None if self.bias is None else self.bias.detach().float().contiguous()
+        y = ops.convtranspose1d_nlc(xn, self.packed(prec), bias, K, u, prec)
+        return ops.nlc_to_ncl(y, x.dtype if x.dtype in (torch.float32, torch.bfloat16) else torch.float32)
+
+
+def _select_activation1d(h):
+    # reference bigvgan.py:94-102: lazy import of the cuda flavour when requested.  Both flavours are the same
+    # fused kernel here; the import keeps `use_cuda_kernel=True` construction paths identical.
+    if h.get("use_cuda_kernel", False):
+        from .alias_free_activation.cuda.activation1d import Activation1d as CudaActivation1d
+        return CudaActivation1d
+    return TorchActivation1d
+
+
+def _make_activations(h, channels, n, activation, Activation1d):
+    if activation == "snake":
+        return nn.ModuleList([Activation1d(activation=activations.Snake(channels, alpha_logscale=h.snake_logscale))
+                              for _ in range(n)])
+    if activation == "snakebeta":
+        return nn.ModuleList([Activation1d(activation=activations.SnakeBeta(channels, alpha_logscale=h.snake_logscale))
+                              for _ in range(n)])
+    raise NotImplementedError(
+        "activation incorrectly specified. check the config file and look for 'activation'.")
+
+
+def _block_precision(block) -> int:
+    return ops.precision_code(getattr(block, "bvg_precision", None) or DEFAULT_PRECISION)
+
+
+class AMPBlock1(torch.nn.Module):
+    """Reference bigvgan.py:31-147.  ``forward`` (:132-141) runs act -> conv(d) -> act -> conv(1) -> +x three times
+    through the libbvg kernels in channels-last layout; the residual add is fused into the second conv's epilogue."""
+
+    def __init__(self, h: AttrDict, channels: int, kernel_size: int = 3, dilation: tuple = (1, 3, 5),
+                 activation: str = None):
+        super().__init__()
+        self.h = h
+        self.convs1 = nn.ModuleList([
+            weight_norm(Conv1d(channels, channels, kernel_size, stride=1, dilation=d,
+                               padding=get_padding(kernel_size, d))) for d in dilation])
+        self.convs1.apply(init_weights)
+        self.convs2 = nn.ModuleList([
+            weight_norm(Conv1d(channels, channels, kernel_size, stride=1, dilation=1,
+                               padding=get_padding(kernel_size, 1))) for _ in range(len(dilation))])
+        self.convs2.apply(init_weights)
+        self.num_layers = len(self.convs1) + len(self.convs2)
+        self.activations = _make_activations(h, channels, self.num_layers, activation, _select_activation1d(self.h))
+
+    def forward(self, x):
+        prec = _block_precision(self)
+        tc = prec == _lib.BVG_BF16_TC
+        op_dtype = torch.bfloat16 if tc else torch.float32
+        xr = ops.ncl_to_nlc(x, torch.float32)  # fp32 residual stream
+        acts1, acts2 = self.activations[::2], self.activations[1::2]
+        for c1, c2, a1, a2 in zip(self.convs1, self.convs2, acts1, acts2):
+            al1, be1 = (t.float().contiguous() for t in a1.log_params())
+            al2, be2 = (t.float().contiguous() for t in a2.log_params())
+            b1 = None if c1.bias is None else c1.bias.detach().float().contiguous()
+            b2 = None if c2.bias is None else c2.bias.detach().float().contiguous()
+            xt = ops.activation1d_nlc(xr, al1, be1, op_dtype, not tc)
+            xt = ops.conv1d_nlc(xt, c1.packed(prec), b1, c1.dilation[0], prec, out_f32=not tc, out_bf16=tc)
+            xt = ops.activation1d_nlc(xt, al2, be2, op_dtype, not tc)
+            xr = ops.conv1d_nlc(xt, c2.packed(prec), b2, 1, prec, residual=xr)
+        return ops.nlc_to_ncl(xr, x.dtype if x.dtype in (torch.float32, torch.bfloat16) else torch.float32)
+
+    def remove_weight_norm(self):
+        for l in self.convs1:
+            remove_weight_norm(l)
+        for l in self.convs2:
+            remove_weight_norm(l)
+
+
+class AMPBlock2(torch.nn.Module):
+    """Reference bigvgan.py:150-240 (one conv per dilation).  Not used by ``bigvgan_v2_22khz_80band_256x``
+    (config.json:2 ``resblock "1"``).  NOTE: the reference copy's ``forward`` lacks ``return x`` (:232-236) and so
+    returns ``None``; this implementation returns the tensor like upstream BigVGAN."""
+
+    def __init__(self, h: AttrDict, channels: int, kernel_size: int = 3, dilation: tuple = (1, 3, 5),
+                 activation: str = None):
+        super().__init__()
+        self.h = h
+        self.convs = nn.ModuleList([
+            weight_norm(Conv1d(channels, channels, kernel_size, stride=1, dilation=d,
+                               padding=get_padding(kernel_size, d))) for d in dilation])
+        self.convs.apply(init_weights)
+        self.num_layers = len(self.convs)
+        self.activations = _make_activations(h, channels, self.num_layers, activation, _select_activation1d(self.h))
+
+    def forward(self, x):
+        prec = _block_precision(self)
+        tc = prec == _lib.BVG_BF16_TC
+        op_dtype = torch.bfloat16 if tc else torch.float32
+        xr = ops.ncl_to_nlc(x, torch.float32)
+        for c, a in zip(self.convs, self.activations):
+            al, be = (t.float().contiguous() for t in a.log_params())
+            b = None if c.bias is None else c.bias.detach().float().contiguous()
+            xt = ops.activation1d_nlc(xr, al, be, op_dtype, not tc)
+            xr = ops.conv1d_nlc(xt, c.packed(prec), b, c.dilation[0], prec, residual=xr)
+        return ops.nlc_to_ncl(xr, x.dtype if x.dtype in (torch.float32, torch.bfloat16) else torch.float32)
+
+    def remove_weight_norm(self):
+        for l in self.convs:
+            remove_weight_norm(l)
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# whole-generator launch plan
+# ---------------------------------------------------------------------------------------------------------------
+_PLANS: "weakref.WeakValueDictionary[int, _PackedGenerator]" = weakref.WeakValueDictionary()
+_next_plan_id = [1]
+
+
+class _PackedGenerator:
+    """Folded + packed weights of one BigVGAN on one device in one precision, and the C descriptor pointing at them."""
+
+    def __init__(self, model: "BigVGAN", device: torch.device, precision: int):
+        h = model.h
+        self.device = device
+        self.precision = precision
+        self.keep = []  # tensors the descriptor points into
+        self.hop = 1
+        for u in h.upsample_rates:
+            self.hop *= int(u)
+        d = _lib.ModelDesc()
+        d.num_mels = int(h.num_mels)
+        d.upsample_initial_channel = int(h.upsample_initial_channel)
+        d.num_stages = model.num_upsamples
+        d.num_kernels = model.num_kernels
+        dil = h.resblock_dilation_sizes
+        if len({len(x) for x in dil}) != 1:
+            raise NotImplementedError("resblock_dilation_sizes must have the same length for every kernel size")
+        d.num_dilations = len(dil[0])
+        if d.num_stages > _lib.MAX_STAGES or d.num_kernels > _lib.MAX_KERNELS or d.num_dilations > _lib.MAX_DILATIONS:
+            raise NotImplementedError("generator larger than the libbvg descriptor limits")
+        for i, (u, k) in enumerate(zip(h.upsample_rates, h.upsample_kernel_sizes)):
+            d.upsample_rates[i] = int(u)
+            d.upsample_kernel_sizes[i] = int(k)
+        d.use_tanh_at_final = int(bool(model.use_tanh_at_final))
+        d.precision = precision
+
+        def f32(t):
+            t = t.detach().to(device=device, dtype=torch.float32).contiguous()
+            self.keep.append(t)
+            return t
+
+        def conv(dst, m, transposed=False):
+            w = m.packed(precision)
+            self.keep.append(w)
+            dst.w = w.data_ptr()
+            dst.bias = f32(m.bias).data_ptr() if m.bias is not None else None
+            dst.cin, dst.cout = int(m.in_channels), int(m.out_channels)
+            dst.k = int(m.kernel_size[0])
+            dst.dilation = int(m.dilation[0])
+
+        def act(dst, a):
+            al, be = a.log_params()
+            dst.alpha_log = f32(al).data_ptr()
+            dst.beta_log = f32(be).data_ptr()
+
+        conv(d.conv_pre, model.conv_pre)
+        for i in range(model.num_upsamples):
+            if len(model.ups[i]) != 1:
+                raise NotImplementedError("one transposed conv per upsample stage expected")
+            conv(d.ups[i], model.ups[i][0], transposed=True)
+            for j in range(model.num_kernels):
+                rb = model.resblocks[i * model.num_kernels + j]
+                if not isinstance(rb, AMPBlock1):
+                    raise NotImplementedError("the fused generator plan implements resblock '1' (AMPBlock1); "
+                                              "AMPBlock2 is available as a standalone module only")
+                for l in range(d.num_dilations):
+                    conv(d.convs1[i][j][l], rb.convs1[l])
+                    conv(d.convs2[i][j][l], rb.convs2[l])
+                for a in range(2 * d.num_dilations):
+                    act(d.acts[i][j][a], rb.activations[a])
+        act(d.act_post, model.activation_post)
+        cp = model.conv_post
+        w_post = f32(_effective_weight(cp))
+        d.conv_post.w = w_post.data_ptr()
+        d.conv_post.bias = f32(cp.bias).data_ptr() if cp.bias is not None else None
+        d.conv_post.cin, d.conv_post.cout = int(cp.in_channels), int(cp.out_channels)
+        d.conv_post.k, d.conv_post.dilation = int(cp.kernel_size[0]), 1
+        self.desc = d
+        self.plan_id = _next_plan_id[0]
+        _next_plan_id[0] += 1
+        _PLANS[self.plan_id] = self
+
+    def run(self, mel: torch.Tensor) -> torch.Tensor:
+        lib = _lib.load()
+        B, _, T = mel.shape
+        wav = torch.empty((B, 1, T * self.hop), dtype=torch.float32, device=mel.device)
+        if B == 0 or T == 0:
+            return wav
+        if mel.stride(2) != 1:
+            mel = mel.contiguous()
+        ws_bytes = lib.bvg_workspace_bytes(ctypes.byref(self.desc), B, T)
+        if ws_bytes == 0:
+            _lib.check(-1, "bvg_workspace_bytes")
+        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=mel.device)  # per call: safe across host threads
+        with torch.cuda.device(mel.device):
+            _lib.check(lib.bvg_forward(ctypes.byref(self.desc), mel.data_ptr(), mel.stride(0), mel.stride(1),
+                                       wav.data_ptr(), B, T, ws.data_ptr(), ws_bytes,
+                                       torch.cuda.current_stream().cuda_stream), "bvg_forward")
+        return wav
+
+
+@torch.library.custom_op("bvg::vocoder_forward", mutates_args=())
+def _vocoder_forward(mel: torch.Tensor, plan_id: int, hop: int) -> torch.Tensor:
+    plan = _PLANS.get(plan_id)
+    if plan is None:
+        raise _lib.BvgError(f"bvg::vocoder_forward: plan {plan_id} no longer exists")
+    return plan.run(mel)
+
+
+@_vocoder_forward.register_fake
+def _(mel, plan_id, hop):
+    return mel.new_empty((mel.shape[0], 1, mel.shape[2] * hop), dtype=torch.float32)
+
+
+class BigVGAN(
+    torch.nn.Module,
+    PyTorchModelHubMixin,
+    library_name="bigvgan",
+    repo_url="https://github.com/NVIDIA/BigVGAN",
+    docs_url="https://github.com/NVIDIA/BigVGAN/blob/main/README.md",
+    pipeline_tag="audio-to-audio",
+    license="mit",
+    tags=["neural-vocoder", "audio-generation", "arxiv:2206.04658"],
+):
+    """Reference bigvgan.py:243-492.
+
+    Args:
+        h (AttrDict): hyper-parameters (``config.json``); mutated like the reference: ``h["use_cuda_kernel"]``.
+        use_cuda_kernel (bool): accepted and stored; both values run the sm_100a kernels (no torch path exists).
+
+    Extra (not in the reference): ``set_precision("bf16" | "fp32")``; default from ``$BVG_PRECISION`` or "bf16"
+    (bf16 tensor-core convs with fp32 accumulation / residual stream / activation math; "fp32" is the exact
+    parity mode).
+    """
+
+    def __init__(self, h: AttrDict, use_cuda_kernel: bool = False):
+        super().__init__()
+        self.h = h
+        self.h["use_cuda_kernel"] = use_cuda_kernel
+        Activation1d = _select_activation1d(self.h)
+
+        self.num_kernels = len(h.resblock_kernel_sizes)
+        self.num_upsamples = len(h.upsample_rates)
+
+        self.conv_pre = weight_norm(Conv1d(h.num_mels, h.upsample_initial_channel, 7, 1, padding=3))
+
+        if h.resblock == "1":
+            resblock_class = AMPBlock1
+        elif h.resblock == "2":
+            resblock_class = AMPBlock2
+        else:
+            raise ValueError(f"Incorrect resblock class specified in hyperparameters. Got {h.resblock}")
+
+        self.ups = nn.ModuleList()
+        for i, (u, k) in enumerate(zip(h.upsample_rates, h.upsample_kernel_sizes)):
+            self.ups.append(nn.ModuleList([
+                weight_norm(ConvTranspose1d(h.upsample_initial_channel // (2 ** i),
+                                            h.upsample_initial_channel // (2 ** (i + 1)), k, u, padding=(k - u) // 2))
+            ]))
+
+        self.resblocks = nn.ModuleList()
+        for i in range(len(self.ups)):
+            ch = h.upsample_initial_channel // (2 ** (i + 1))
+            for j, (k, d) in enumerate(zip(h.resblock_kernel_sizes, h.resblock_dilation_sizes)):
+                self.resblocks.append(resblock_class(h, ch, k, d, activation=h.activation))
+
+        activation_post = (
+            activations.Snake(ch, alpha_logscale=h.snake_logscale) if h.activation == "snake"
+            else (activations.SnakeBeta(ch, alpha_logscale=h.snake_logscale) if h.activation == "snakebeta" else None))
+        if activation_post is None:
+            raise NotImplementedError(
+                "activation incorrectly specified. check the config file and look for 'activation'.")
+        self.activation_post = Activation1d(activation=activation_post)
+
+        self.use_bias_at_final = h.get("use_bias_at_final", True)
+        self.conv_post = weight_norm(Conv1d(ch, 1, 7, 1, padding=3, bias=self.use_bias_at_final))
+
+        for i in range(len(self.ups)):
+            self.ups[i].apply(init_weights)
+        self.conv_post.apply(init_weights)
+
+        self.use_tanh_at_final = h.get("use_tanh_at_final", True)
+        self.__dict__["_bvg_precision"] = DEFAULT_PRECISION
+        self.__dict__["_bvg_plan"] = None
+        self.__dict__["_bvg_plan_key"] = None
+
+    # ---- libbvg plumbing ---------------------------------------------------------------------------------
+    def set_precision(self, precision: str) -> "BigVGAN":
+        ops.precision_code(precision)
+        self.__dict__["_bvg_precision"] = precision
+        for m in self.modules():
+            if isinstance(m, (Conv1d, ConvTranspose1d, AMPBlock1, AMPBlock2)):
+                m.bvg_precision = precision
+        return self
+
+    @property
+    def precision(self) -> str:
+        return self.__dict__["_bvg_precision"]
+
+    def _plan(self, device: torch.device) -> _PackedGenerator:
+        prec = ops.precision_code(self.__dict__["_bvg_precision"])
+        key = (device, prec, tuple((p.data_ptr(), p._version) for p in self.parameters()))
+        if self.__dict__["_bvg_plan"] is None or self.__dict__["_bvg_plan_key"] != key:
+            for p in self.parameters():
+                if p.device != device:
+                    raise _lib.BvgError(f"BigVGAN parameters live on {p.device} but the input is on {device}; "
+                                        "call .to(device) first")
+            self.__dict__["_bvg_plan"] = _PackedGenerator(self, device, prec)
+            self.__dict__["_bvg_plan_key"] = key
+        return self.__dict__["_bvg_plan"]
+
+    def forward(self, x):
+        """``[B, num_mels, T_mel]`` CUDA tensor -> ``[B, 1, T_mel * hop]`` fp32 in [-1, 1] (reference :360-386)."""
+        if x.dim() != 3 or x.shape[1] != self.h.num_mels:
+            raise ValueError(f"expected mel of shape [B, {self.h.num_mels}, T], got {tuple(x.shape)}")
+        if not x.is_cuda:
+            raise _lib.BvgError("BigVGAN.forward: libbvg has no CPU path; move the module and the mel to a B200 "
+                                f"(got device {x.device})")
+        _lib.require_device(x.device.index if x.device.index is not None else torch.cuda.current_device())
+        if x.dtype != torch.float32:
+            x = x.float()
+        plan = self._plan(x.device)
+        return _vocoder_forward(x, plan.plan_id, plan.hop)
+
+    def remove_weight_norm(self):
+        try:
+            print("Removing weight norm...")
+            for l in self.ups:
+                for l_i in l:
+                    remove_weight_norm(l_i)
+            for l in self.resblocks:
+                l.remove_weight_norm()
+            remove_weight_norm(self.conv_pre)
+            remove_weight_norm(self.conv_post)
+        except ValueError:
+            print("[INFO] Model already removed weight norm. Skipping!")
+            pass
+
+    # ---- huggingface_hub support (reference bigvgan.py:403-492) ---------------------------------------------
+    def _save_pretrained(self, save_directory: Path) -> None:
+        model_path = save_directory / "bigvgan_generator.pt"
+        torch.save({"generator": self.state_dict()}, model_path)
+        config_path = save_directory / "config.json"
+        with open(config_path, "w") as config_file:
+            json.dump(self.h, config_file, indent=4)
+
+    @classmethod
+    def _from_pretrained(
+            cls,
+            *,
+            model_id: str,
+            revision: str = None,
+            cache_dir: str = None,
+            force_download: bool = False,
+            proxies: Optional[Dict] = None,
+            resume_download: bool = False,
+            local_files_only: bool = False,
+            token: Union[str, bool, None] = None,
+            map_location: str = "cpu",
+            strict: bool = False,
+            use_cuda_kernel: bool = False,
+            **model_kwargs,
+    ):
+        if os.path.isdir(model_id):
+            print("Loading config.json from local directory")
+            config_file = os.path.join(model_id, "config.json")
+        else:
+            config_file = hf_hub_download(repo_id=model_id, filename="config.json", revision=revision,
+                                          cache_dir=cache_dir, force_download=force_download, proxies=proxies,
+                                          resume_download=resume_download, token=token,
+                                          local_files_only=local_files_only)
+        h = load_hparams_from_json(config_file)
+        model = cls(h, use_cuda_kernel=use_cuda_kernel)
+        if os.path.isdir(model_id):
+            print("Loading weights from local directory")
+            model_file = os.path.join(model_id, "bigvgan_generator.pt")
+        else:
+            print(f"Loading weights from {model_id}")
+            model_file = hf_hub_download(repo_id=model_id, filename="bigvgan_generator.pt", revision=revision,
+                                         cache_dir=cache_dir, force_download=force_download, proxies=proxies,
+                                         resume_download=resume_download, token=token,
+                                         local_files_only=local_files_only)
+        checkpoint_dict = torch.load(model_file, map_location=map_location)
+        try:
+            model.load_state_dict(checkpoint_dict["generator"])
+        except RuntimeError:
+            print("[INFO] the pretrained checkpoint does not contain weight norm. Loading the checkpoint after "
+                  "removing weight norm!")
+            model.remove_weight_norm()
+            model.load_state_dict(checkpoint_dict["generator"])
+        return model

@@ -1,0 +1,484 @@
+// Fused anti-aliased SnakeBeta activation (Activation1d): y = lowpass_down2( snake_beta( up2(x) ) ).
+//
+// Replaces the reference's fused extension kernel (alias_free_activation/cuda/anti_alias_activation_cuda.cu:43-179)
+// and its torch path (alias_free_activation/torch/act.py:25-30, resample.py:30-38, filter.py:94-101,
+// activations.py:107-120).  Written from the closed forms, cl() = clamp to [0,T-1]:
+//     u[2m]   = sum_j E_even[j] x[cl(m+j)]   j=-3..2     (E = 2*f, polyphase up-sampler, gain 2 folded in)
+//     u[2m+1] = sum_j E_odd[j]  x[cl(m+j)]   j=-2..3
+//     v[n]    = u[n] + 1/(exp(beta)+1e-9) * sin^2(exp(alpha) * u[n])
+//     y[i]    = sum_{k<12} f[k] v[clamp(2i+k-5, 0, 2T-1)]
+// No 2x-rate tensor is ever written: the 2x signal lives in registers.
+//
+// Two kernels:
+//  * act1d_nlc_kernel  -- internal channels-last layout [B,T,C].  One thread owns a channel PAIR and marches along
+//    time with register sliding windows, so every FIR/snake op is a packed f32x2 instruction (FFMA2) over the two
+//    channels and each input element is loaded exactly once (plus a 6-row warm-up per time segment).  Loads and
+//    stores are coalesced across the channel axis.
+//  * act1d_ncl_kernel  -- public [B,C,T] layout.  A CTA stages a halo'd time tile of one (b,c) row in shared
+//    memory with one bulk asynchronous copy (TMA engine, cp.async.bulk + mbarrier), each thread computes 16
+//    consecutive outputs from registers and writes them with 128-bit stores.
+#include "bvg_common.cuh"
+#include "sm100_ptx.cuh"
+
+namespace bvg {
+
+__device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) { return __ffma2_rn(a, b, c); }
+__device__ __forceinline__ float2 fmul2(float2 a, float2 b) { return __fmul2_rn(a, b); }
+__device__ __forceinline__ float2 fadd2(float2 a, float2 b) { return __fadd2_rn(a, b); }
+__device__ __forceinline__ float2 splat(float a) { return make_float2(a, a); }
+
+// Per-channel-pair snake constants.
+struct SnakeCoef {
+    float2 a;     // exp(alpha)               (precise)   | 2*exp(alpha)            (fast)
+    float2 invb;  // 1/(exp(beta)+1e-9)       (precise)   | 0.5/(exp(beta)+1e-9)    (fast)
+};
+
+template <bool PRECISE>
+__device__ __forceinline__ SnakeCoef make_coef(float al0, float al1, float be0, float be1) {
+    SnakeCoef c;
+    float a0 = expf(al0), a1 = expf(al1);
+    float b0 = 1.0f / (expf(be0) + 1e-9f), b1 = 1.0f / (expf(be1) + 1e-9f);
+    if (PRECISE) {
+        c.a = make_float2(a0, a1);
+        c.invb = make_float2(b0, b1);
+    } else {
+        c.a = make_float2(2.0f * a0, 2.0f * a1);
+        c.invb = make_float2(0.5f * b0, 0.5f * b1);
+    }
+    return c;
+}
+
+// PRECISE: v = u + invb * sin(a u)^2 (libdevice sinf, full range reduction).
+// fast   : sin^2(t) = (1 - cos 2t)/2  ->  v = u - c*cos(2a u) + c with c = invb/2; the constant "+c" is NOT added
+//          here: the down filter has unit DC gain and replicate padding, so it is added once per output instead.
+template <bool PRECISE>
+__device__ __forceinline__ float2 snake2(float2 u, const SnakeCoef& c) {
+    if (PRECISE) {
+        float s0 = sinf(u.x * c.a.x), s1 = sinf(u.y * c.a.y);
+        return make_float2(fmaf(c.invb.x, s0 * s0, u.x), fmaf(c.invb.y, s1 * s1, u.y));
+    } else {
+        float2 t = fmul2(u, c.a);
+        float2 cs = make_float2(__cosf(t.x), __cosf(t.y));
+        return ffma2(make_float2(-c.invb.x, -c.invb.y), cs, u);
+    }
+}
+
+template <typename T>
+struct PairIO;
+template <>
+struct PairIO<float> {
+    static __device__ __forceinline__ float2 load(const float* p) { return __ldg(reinterpret_cast<const float2*>(p)); }
+    static __device__ __forceinline__ void store(float* p, float2 v) { *reinterpret_cast<float2*>(p) = v; }
+};
+template <>
+struct PairIO<__nv_bfloat16> {
+    static __device__ __forceinline__ float2 load(const __nv_bfloat16* p) {
+        unsigned int raw = __ldg(reinterpret_cast<const unsigned int*>(p));
+        return make_float2(__uint_as_float(raw << 16), __uint_as_float(raw & 0xffff0000u));
+    }
+    static __device__ __forceinline__ void store(__nv_bfloat16* p, float2 v) {
+        *reinterpret_cast<__nv_bfloat162*>(p) = __float22bfloat162_rn(v);
+    }
+};
+
+// ------------------------------------------------------------------------------------------------------------
+// channels-last kernel
+// ------------------------------------------------------------------------------------------------------------
+// Thread (pair, seg) produces y[b, seg*L .. seg*L+L-1, 2*pair .. 2*pair+1].  L + 6 must be a multiple of 7.
+// EDGE = false: the segment and its +-6-row halo lie strictly inside [0,T): no clamping, no padding logic.
+// EDGE = true: first / last segments of a sequence (replicate padding of x and of the activated 2x signal).
+struct ActEdge {
+    int rel_lo, rel_hi;  // row 0 and row T-1 relative to row t0-6 (capped)
+    int m_valid;         // steps g < m_valid have pair index m < T
+    int n_out;           // outputs of this segment
+    bool first_seg;      // t0 == 0
+};
+
+// One 7-step body: consumes cur[0..6] (rows rel 6+g0 .. 12+g0), produces outputs rel rows g0-6 .. g0.
+template <typename TOut, bool PRECISE, bool EDGE, bool FIRST>
+__device__ __forceinline__ void act1d_nlc_body(float2 (&xw)[7], float2 (&ve)[7], float2 (&vo)[7],
+                                               const float2 (&cur)[7], float2& vlast, const SnakeCoef& coef,
+                                               const ActEdge& e, int g0, TOut* __restrict__ yrel, int64_t C) {
+    const float2 E0 = splat(2.f * BVG_F0), E1 = splat(2.f * BVG_F1), E2 = splat(2.f * BVG_F2),
+                 E3 = splat(2.f * BVG_F3), E4 = splat(2.f * BVG_F4), E5 = splat(2.f * BVG_F5);
+    const float2 G0 = splat(BVG_F0), G1 = splat(BVG_F1), G2 = splat(BVG_F2), G3 = splat(BVG_F3), G4 = splat(BVG_F4),
+                 G5 = splat(BVG_F5);
+    const float2 hoisted_c = PRECISE ? splat(0.f) : coef.invb;
+#pragma unroll
+    for (int s = 0; s < 7; ++s) {
+        const int g = g0 + s;
+        xw[(s + 6) % 7] = cur[s];
+        const float2 xm3 = xw[(s + 0) % 7], xm2 = xw[(s + 1) % 7], xm1 = xw[(s + 2) % 7], x0 = xw[(s + 3) % 7],
+                     xp1 = xw[(s + 4) % 7], xp2 = xw[(s + 5) % 7], xp3 = xw[(s + 6) % 7];
+        float2 ue = fmul2(E0, xm3);
+        ue = ffma2(E2, xm2, ue);
+        ue = ffma2(E4, xm1, ue);
+        ue = ffma2(E5, x0, ue);
+        ue = ffma2(E3, xp1, ue);
+        ue = ffma2(E1, xp2, ue);
+        float2 uo = fmul2(E1, xm2);
+        uo = ffma2(E3, xm1, uo);
+        uo = ffma2(E5, x0, uo);
+        uo = ffma2(E4, xp1, uo);
+        uo = ffma2(E2, xp2, uo);
+        uo = ffma2(E0, xp3, uo);
+        float2 a = snake2<PRECISE>(ue, coef);
+        float2 o = snake2<PRECISE>(uo, coef);
+        if (EDGE) {
+            if (g >= e.m_valid) {  // m >= T: replicate padding of the 2x signal on the right: v[2T-1]
+                a = vlast;
+                o = vlast;
+            } else {
+                vlast = o;
+            }
+        }
+        ve[s] = a;
+        vo[s] = o;
+        if (EDGE && FIRST && s == 3 && e.first_seg) {  // m == 0: replicate padding on the left: v[0]
+            ve[0] = vo[0] = ve[1] = vo[1] = ve[2] = vo[2] = a;
+        }
+        if (!FIRST || s == 6) {
+            const int i = g - 6;  // output row relative to t0
+            float2 acc = fmul2(G0, vo[(s + 1) % 7]);
+            acc = ffma2(G1, ve[(s + 2) % 7], acc);
+            acc = ffma2(G2, vo[(s + 2) % 7], acc);
+            acc = ffma2(G3, ve[(s + 3) % 7], acc);
+            acc = ffma2(G4, vo[(s + 3) % 7], acc);
+            acc = ffma2(G5, ve[(s + 4) % 7], acc);
+            acc = ffma2(G5, vo[(s + 4) % 7], acc);
+            acc = ffma2(G4, ve[(s + 5) % 7], acc);
+            acc = ffma2(G3, vo[(s + 5) % 7], acc);
+            acc = ffma2(G2, ve[(s + 6) % 7], acc);
+            acc = ffma2(G1, vo[(s + 6) % 7], acc);
+            acc = ffma2(G0, ve[s], acc);
+            if (!PRECISE) acc = fadd2(acc, hoisted_c);
+            if (!EDGE || i < e.n_out) PairIO<TOut>::store(yrel + (int64_t)i * C, acc);
+        }
+    }
+}
+
+template <typename TIn, typename TOut, bool PRECISE, bool EDGE>
+__device__ __forceinline__ void act1d_nlc_segment(const TIn* __restrict__ xb, TOut* __restrict__ yb,
+                                                  const SnakeCoef& coef, int64_t T, int C, int L, int64_t t0) {
+    // rows are addressed relative to row (t0 - 6): rel = row - (t0 - 6)
+    const TIn* xrel = xb + (t0 - 6) * C;
+    TOut* yrel = yb + t0 * C;
+    ActEdge e;
+    e.rel_lo = EDGE ? (int)(6 - t0 > 0 ? 6 - t0 : 0) : 0;
+    e.rel_hi = EDGE ? (int)min((int64_t)(L + 64), T - 1 - (t0 - 6)) : 0;
+    e.m_valid = EDGE ? (int)min((int64_t)(L + 64), T - (t0 - 3)) : 0;
+    e.n_out = (int)min((int64_t)L, T - t0);
+    e.first_seg = (t0 == 0);
+    auto ldx = [&](int rel) -> float2 {
+        if (EDGE) rel = rel < e.rel_lo ? e.rel_lo : (rel > e.rel_hi ? e.rel_hi : rel);
+        return PairIO<TIn>::load(xrel + (int64_t)rel * C);
+    };
+    // x window: x[m+j], j=-3..3, lives in xw[(s+j+3)%7] at step s of a 7-step body; pair m in ve/vo[s].
+    float2 xw[7], ve[7], vo[7], cur[7], nxt[7];
+    float2 vlast = splat(0.f);
+#pragma unroll
+    for (int j = 0; j < 6; ++j) xw[j] = ldx(j);
+#pragma unroll
+    for (int s = 0; s < 7; ++s) {
+        cur[s] = ldx(6 + s);
+        ve[s] = vo[s] = splat(0.f);
+    }
+    const int nbody = (L + 6) / 7;
+    if (nbody > 1) {
+#pragma unroll
+        for (int s = 0; s < 7; ++s) nxt[s] = ldx(13 + s);
+    }
+    act1d_nlc_body<TOut, PRECISE, EDGE, true>(xw, ve, vo, cur, vlast, coef, e, 0, yrel, C);
+#pragma unroll 1
+    for (int body = 1; body < nbody; ++body) {
+        const int g0 = 7 * body;
+#pragma unroll
+        for (int s = 0; s < 7; ++s) cur[s] = nxt[s];
+        if (body + 1 < nbody) {
+#pragma unroll
+            for (int s = 0; s < 7; ++s) nxt[s] = ldx(g0 + 13 + s);
+        }
+        act1d_nlc_body<TOut, PRECISE, EDGE, false>(xw, ve, vo, cur, vlast, coef, e, g0, yrel, C);
+    }
+}
+
+// grid = (ceil(n_seg / segs_per_block), C/2 / S, B); block = S * segs_per_block threads.
+template <typename TIn, typename TOut, bool PRECISE>
+__global__ void __launch_bounds__(256)
+act1d_nlc_kernel(const TIn* __restrict__ x, TOut* __restrict__ y, const float* __restrict__ alpha,
+                 const float* __restrict__ beta, int64_t T, int C, int L, int S, int64_t n_seg) {
+    const int pair = blockIdx.y * S + (threadIdx.x % S);
+    const int64_t seg = (int64_t)blockIdx.x * (blockDim.x / S) + (threadIdx.x / S);
+    if (seg >= n_seg) return;
+    const int64_t b = blockIdx.z;
+    const int64_t t0 = seg * L;
+    const TIn* xb = x + (b * T) * C + 2 * pair;
+    TOut* yb = y + (b * T) * C + 2 * pair;
+    const SnakeCoef coef = make_coef<PRECISE>(alpha[2 * pair], alpha[2 * pair + 1], beta[2 * pair], beta[2 * pair + 1]);
+    // the segment's loads touch rows t0-6 .. t0+L+5 (the last 7-row prefetch is skipped)
+    const bool interior = (t0 >= 6) && (t0 + L + 6 <= T);
+    if (interior)
+        act1d_nlc_segment<TIn, TOut, PRECISE, false>(xb, yb, coef, T, C, L, t0);
+    else
+        act1d_nlc_segment<TIn, TOut, PRECISE, true>(xb, yb, coef, T, C, L, t0);
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// [B,C,T] kernel with a TMA-staged halo'd time tile
+// ------------------------------------------------------------------------------------------------------------
+constexpr int NCL_THREADS = 128;
+constexpr int NCL_PER_THREAD = 16;
+constexpr int NCL_TILE = NCL_THREADS * NCL_PER_THREAD;  // 2048 outputs per CTA
+constexpr int NCL_HALO = 8;                             // >= 6; multiple of 8 keeps interior tiles 16-byte aligned
+constexpr int NCL_SMEM_ELEMS = NCL_TILE + 2 * NCL_HALO + 16;
+
+__device__ __forceinline__ void bulk_copy_g2s(void* smem_dst, const void* gmem_src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(smem_dst)), "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+
+template <typename TIO>
+struct NclIO;
+template <>
+struct NclIO<float> {
+    // xr[j] = tile[base + j], j < 32, base % 4 == 0
+    static __device__ __forceinline__ void load32(const float* tile, int base, float (&xr)[32]) {
+        const float4* p = reinterpret_cast<const float4*>(tile + base);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            float4 v = p[j];
+            xr[4 * j] = v.x; xr[4 * j + 1] = v.y; xr[4 * j + 2] = v.z; xr[4 * j + 3] = v.w;
+        }
+    }
+    static __device__ __forceinline__ float get(const float* tile, int i) { return tile[i]; }
+    static __device__ __forceinline__ void store16(float* y, const float (&o)[16]) {
+        float4* p = reinterpret_cast<float4*>(y);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) p[j] = make_float4(o[4 * j], o[4 * j + 1], o[4 * j + 2], o[4 * j + 3]);
+    }
+    static __device__ __forceinline__ void store1(float* y, float v) { *y = v; }
+};
+template <>
+struct NclIO<__nv_bfloat16> {
+    static __device__ __forceinline__ void load32(const __nv_bfloat16* tile, int base, float (&xr)[32]) {
+        const uint4* p = reinterpret_cast<const uint4*>(tile + base);  // base % 8 == 0
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            uint4 v = p[j];
+            const unsigned int w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                xr[8 * j + 2 * q] = __uint_as_float(w[q] << 16);
+                xr[8 * j + 2 * q + 1] = __uint_as_float(w[q] & 0xffff0000u);
+            }
+        }
+    }
+    static __device__ __forceinline__ float get(const __nv_bfloat16* tile, int i) { return __bfloat162float(tile[i]); }
+    static __device__ __forceinline__ void store16(__nv_bfloat16* y, const float (&o)[16]) {
+        uint4* p = reinterpret_cast<uint4*>(y);
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            __nv_bfloat162 h0 = __floats2bfloat162_rn(o[8 * j], o[8 * j + 1]);
+            __nv_bfloat162 h1 = __floats2bfloat162_rn(o[8 * j + 2], o[8 * j + 3]);
+            __nv_bfloat162 h2 = __floats2bfloat162_rn(o[8 * j + 4], o[8 * j + 5]);
+            __nv_bfloat162 h3 = __floats2bfloat162_rn(o[8 * j + 6], o[8 * j + 7]);
+            p[j] = make_uint4(*reinterpret_cast<unsigned int*>(&h0), *reinterpret_cast<unsigned int*>(&h1),
+                              *reinterpret_cast<unsigned int*>(&h2), *reinterpret_cast<unsigned int*>(&h3));
+        }
+    }
+    static __device__ __forceinline__ void store1(__nv_bfloat16* y, float v) { *y = __float2bfloat16_rn(v); }
+};
+
+// grid = (ceil(T / NCL_TILE), C, B)
+template <typename TIO, bool PRECISE>
+__global__ void __launch_bounds__(NCL_THREADS)
+act1d_ncl_kernel(const TIO* __restrict__ x, TIO* __restrict__ y, const float* __restrict__ alpha,
+                 const float* __restrict__ beta, int64_t C, int64_t T, int64_t stride_b, int64_t stride_c,
+                 int vec_store_ok) {
+    __shared__ __align__(128) TIO tile[NCL_SMEM_ELEMS];
+    __shared__ __align__(8) uint64_t bar;
+    const int64_t c = blockIdx.y, b = blockIdx.z;
+    const int64_t t0 = (int64_t)blockIdx.x * NCL_TILE;
+    const TIO* row = x + b * stride_b + c * stride_c;
+    const int64_t lo = max(t0 - (int64_t)NCL_HALO, (int64_t)0);
+    const int64_t hi = min(t0 + (int64_t)(NCL_TILE + NCL_HALO), T);
+    const uintptr_t a_lo = reinterpret_cast<uintptr_t>(row + lo), a_hi = reinterpret_cast<uintptr_t>(row + hi);
+    const uintptr_t c_lo = a_lo & ~uintptr_t(15), c_hi = (a_hi + 15) & ~uintptr_t(15);
+    const int delta = static_cast<int>((a_lo - c_lo) / sizeof(TIO));
+
+    if (threadIdx.x == 0) {
+        mbar_init(&bar, 1);
+        fence_barrier_init();
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const uint32_t bytes = static_cast<uint32_t>(c_hi - c_lo);
+        mbar_arrive_expect_tx(&bar, bytes);
+        bulk_copy_g2s(tile, reinterpret_cast<const void*>(c_lo), bytes, &bar);
+    }
+    const SnakeCoef coef = make_coef<PRECISE>(alpha[c], alpha[c], beta[c], beta[c]);
+    mbar_wait(&bar, 0);
+
+    const int64_t i0 = t0 + (int64_t)threadIdx.x * NCL_PER_THREAD;
+    if (i0 >= T) return;
+
+    // xr[j] = x[cl(i0 - 8 + j)]
+    float xr[32];
+    if (delta == 0 && i0 - 8 >= lo && i0 + 24 <= hi) {
+        NclIO<TIO>::load32(tile, static_cast<int>(i0 - 8 - lo), xr);
+    } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+            int64_t idx = i0 - 8 + j;
+            idx = idx < 0 ? 0 : (idx >= T ? T - 1 : idx);
+            xr[j] = NclIO<TIO>::get(tile, delta + static_cast<int>(idx - lo));
+        }
+    }
+
+    const float e0 = 2.f * BVG_F0, e1 = 2.f * BVG_F1, e2 = 2.f * BVG_F2, e3 = 2.f * BVG_F3, e4 = 2.f * BVG_F4,
+                e5 = 2.f * BVG_F5;
+    // v2[p] = (v[2m], v[2m+1]) for m = i0 - 3 + p
+    float2 v2[NCL_PER_THREAD + 6];
+    float vlast = 0.f;
+#pragma unroll
+    for (int p = 0; p < NCL_PER_THREAD + 6; ++p) {
+        // x[m+j] = xr[p + 5 + j]
+        float2 u = fmul2(make_float2(e0, e1), make_float2(xr[p + 2], xr[p + 3]));
+        u = ffma2(make_float2(e2, e3), make_float2(xr[p + 3], xr[p + 4]), u);
+        u = ffma2(make_float2(e4, e5), make_float2(xr[p + 4], xr[p + 5]), u);
+        u = ffma2(make_float2(e5, e4), make_float2(xr[p + 5], xr[p + 6]), u);
+        u = ffma2(make_float2(e3, e2), make_float2(xr[p + 6], xr[p + 7]), u);
+        u = ffma2(make_float2(e1, e0), make_float2(xr[p + 7], xr[p + 8]), u);
+        float2 v = snake2<PRECISE>(u, coef);
+        const int64_t m = i0 - 3 + p;
+        if (m >= T) {
+            v = splat(vlast);
+        } else {
+            vlast = v.y;
+        }
+        v2[p] = v;
+    }
+    if (i0 == 0) {  // m = -3,-2,-1 -> v[0]
+        v2[0] = v2[1] = v2[2] = splat(v2[3].x);
+    }
+    const float hoisted_c = PRECISE ? 0.f : coef.invb.x;
+    float out[NCL_PER_THREAD];
+#pragma unroll
+    for (int q = 0; q < NCL_PER_THREAD; ++q) {
+        float2 acc = fmul2(make_float2(BVG_F1, BVG_F2), v2[q + 1]);
+        acc = ffma2(make_float2(BVG_F3, BVG_F4), v2[q + 2], acc);
+        acc = ffma2(make_float2(BVG_F5, BVG_F5), v2[q + 3], acc);
+        acc = ffma2(make_float2(BVG_F4, BVG_F3), v2[q + 4], acc);
+        acc = ffma2(make_float2(BVG_F2, BVG_F1), v2[q + 5], acc);
+        float r = fmaf(BVG_F0, v2[q].y, acc.x);
+        r = fmaf(BVG_F0, v2[q + 6].x, r);
+        out[q] = r + acc.y + hoisted_c;
+    }
+    TIO* yrow = y + (b * C + c) * T + i0;
+    if (vec_store_ok && i0 + NCL_PER_THREAD <= T) {
+        NclIO<TIO>::store16(yrow, out);
+    } else {
+#pragma unroll
+        for (int q = 0; q < NCL_PER_THREAD; ++q)
+            if (i0 + q < T) NclIO<TIO>::store1(yrow + q, out[q]);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// host launchers
+// ------------------------------------------------------------------------------------------------------------
+template <typename TIn, typename TOut>
+static int launch_nlc(const void* x, void* y, const float* alpha, const float* beta, int64_t B, int64_t T, int64_t C,
+                      int precise, cudaStream_t st) {
+    const int P = static_cast<int>(C / 2);
+    int S = P;
+    if (P > 256) {
+        S = 1;
+        for (int d = 256; d >= 1; --d)
+            if (P % d == 0) { S = d; break; }
+    }
+    const int segs_per_block = S >= 256 ? 1 : 256 / S;
+    // segment length: L + 6 must be a multiple of 7; prefer long segments (6 warm-up rows each) while keeping the
+    // machine full
+    static const int kL[] = {120, 64, 36, 22, 15, 8};
+    int L = 8;
+    for (int cand : kL) {
+        if ((double)B * (double)ceil_div(T, cand) * (double)P >= 148.0 * 1536.0) { L = cand; break; }
+    }
+    const int64_t n_seg = ceil_div(T, L);
+    dim3 grid(static_cast<unsigned>(ceil_div(n_seg, segs_per_block)), static_cast<unsigned>(P / S),
+              static_cast<unsigned>(B));
+    dim3 block(S * segs_per_block);
+    if (precise)
+        act1d_nlc_kernel<TIn, TOut, true><<<grid, block, 0, st>>>(static_cast<const TIn*>(x), static_cast<TOut*>(y),
+                                                                   alpha, beta, T, (int)C, L, S, n_seg);
+    else
+        act1d_nlc_kernel<TIn, TOut, false><<<grid, block, 0, st>>>(static_cast<const TIn*>(x), static_cast<TOut*>(y),
+                                                                    alpha, beta, T, (int)C, L, S, n_seg);
+    BVG_LAUNCH_CHECK("act1d_nlc_kernel");
+    return BVG_OK;
+}
+
+int activation1d_nlc(const void* x, int x_dtype, void* y, int y_dtype, const float* alpha, const float* beta,
+                     int64_t B, int64_t T, int64_t C, int precise, cudaStream_t st) {
+    BVG_REQUIRE(x && y && alpha && beta, BVG_ERR_INVALID, "activation1d_nlc: null pointer");
+    BVG_REQUIRE(B >= 0 && T >= 0 && C > 0, BVG_ERR_INVALID, "activation1d_nlc: bad shape B=%lld T=%lld C=%lld",
+                (long long)B, (long long)T, (long long)C);
+    BVG_REQUIRE(C % 2 == 0, BVG_ERR_UNSUPPORTED, "activation1d_nlc: C=%lld must be even", (long long)C);
+    BVG_REQUIRE(B <= 65535, BVG_ERR_UNSUPPORTED, "activation1d_nlc: B=%lld > 65535", (long long)B);
+    if (B == 0 || T == 0) return BVG_OK;
+    if (x_dtype == BVG_F32 && y_dtype == BVG_BF16)
+        return launch_nlc<float, __nv_bfloat16>(x, y, alpha, beta, B, T, C, precise, st);
+    if (x_dtype == BVG_F32 && y_dtype == BVG_F32) return launch_nlc<float, float>(x, y, alpha, beta, B, T, C, precise, st);
+    if (x_dtype == BVG_BF16 && y_dtype == BVG_BF16)
+        return launch_nlc<__nv_bfloat16, __nv_bfloat16>(x, y, alpha, beta, B, T, C, precise, st);
+    if (x_dtype == BVG_BF16 && y_dtype == BVG_F32)
+        return launch_nlc<__nv_bfloat16, float>(x, y, alpha, beta, B, T, C, precise, st);
+    return set_error(BVG_ERR_UNSUPPORTED, "activation1d_nlc: unsupported dtypes %d -> %d", x_dtype, y_dtype);
+}
+
+template <typename TIO>
+static int launch_ncl(const void* x, void* y, const float* alpha, const float* beta, int64_t B, int64_t C, int64_t T,
+                      int64_t sb, int64_t sc, int precise, cudaStream_t st) {
+    const int vec_ok = ((T * (int64_t)sizeof(TIO)) % 16 == 0) && (reinterpret_cast<uintptr_t>(y) % 16 == 0);
+    dim3 grid(static_cast<unsigned>(ceil_div(T, NCL_TILE)), static_cast<unsigned>(C), static_cast<unsigned>(B));
+    if (precise)
+        act1d_ncl_kernel<TIO, true><<<grid, NCL_THREADS, 0, st>>>(static_cast<const TIO*>(x), static_cast<TIO*>(y),
+                                                                   alpha, beta, C, T, sb, sc, vec_ok);
+    else
+        act1d_ncl_kernel<TIO, false><<<grid, NCL_THREADS, 0, st>>>(static_cast<const TIO*>(x), static_cast<TIO*>(y),
+                                                                    alpha, beta, C, T, sb, sc, vec_ok);
+    BVG_LAUNCH_CHECK("act1d_ncl_kernel");
+    return BVG_OK;
+}
+
+}  // namespace bvg
+
+using namespace bvg;
+
+extern "C" int bvg_activation1d_fwd(const void* x, void* y, const float* alpha_log, const float* beta_log, int64_t B,
+                                    int64_t C, int64_t T, int64_t x_stride_b, int64_t x_stride_c, int dtype,
+                                    int precise, void* stream) {
+    BVG_REQUIRE(x && y && alpha_log && beta_log, BVG_ERR_INVALID, "bvg_activation1d_fwd: null pointer");
+    BVG_REQUIRE(B >= 0 && C >= 0 && T >= 0, BVG_ERR_INVALID, "bvg_activation1d_fwd: negative shape");
+    BVG_REQUIRE(C <= 65535 && B <= 65535, BVG_ERR_UNSUPPORTED, "bvg_activation1d_fwd: B, C must be <= 65535");
+    BVG_REQUIRE(dtype == BVG_F32 || dtype == BVG_BF16, BVG_ERR_UNSUPPORTED,
+                "bvg_activation1d_fwd: dtype %d not supported (fp32 and bf16 only)", dtype);
+    const int64_t es = dtype == BVG_F32 ? 4 : 2;
+    BVG_REQUIRE(reinterpret_cast<uintptr_t>(x) % es == 0 && reinterpret_cast<uintptr_t>(y) % es == 0, BVG_ERR_INVALID,
+                "bvg_activation1d_fwd: pointers not element aligned");
+    BVG_REQUIRE(x_stride_c >= T && x_stride_b >= 0, BVG_ERR_INVALID, "bvg_activation1d_fwd: bad strides");
+    if (B == 0 || C == 0 || T == 0) return BVG_OK;  // like the reference (.cu:193-196): empty input is a no-op
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (dtype == BVG_F32)
+        return launch_ncl<float>(x, y, alpha_log, beta_log, B, C, T, x_stride_b, x_stride_c, precise, st);
+    return launch_ncl<__nv_bfloat16>(x, y, alpha_log, beta_log, B, C, T, x_stride_b, x_stride_c, precise, st);
+}
+
+extern "C" int bvg_activation1d_nlc_fwd(const void* x, int x_dtype, void* y, int y_dtype, const float* alpha_log,
+                                        const float* beta_log, int64_t B, int64_t T, int64_t C, int precise,
+                                        void* stream) {
+    return activation1d_nlc(x, x_dtype, y, y_dtype, alpha_log, beta_log, B, T, C, precise,
+                            static_cast<cudaStream_t>(stream));
+}

@@ -1,0 +1,376 @@
+// Dilated Conv1d / polyphase ConvTranspose1d as an implicit GEMM on tcgen05 tensor cores (sm_100a).
+//
+// Replaces cuDNN/ATen behind nn.Conv1d (reference bigvgan.py:58-66,75-83,285-287) and nn.ConvTranspose1d
+// (bigvgan.py:305-313).  Layout is channels-last ("nlc"): activations [B, T, Cin] bf16, packed weights
+// [taps][Nout][Cin] bf16, so that
+//   D[M = 128 time rows, N = output channels] += A[M, K = 64 input channels] * B[N, K]^T   per tap, per K-block,
+// with both operands K-major in shared memory under the 128-byte swizzle.
+//
+// One halo'd TMA tile serves every tap: the A tile holds rows t0+base .. t0+base+(k-1)*d+127 of the input (TMA
+// zero-fills rows outside [0,T) -> the conv's zero padding, per batch item because the tensor map is 3-D
+// [Cin, T, B]); tap j's operand is the SAME shared memory addressed through a UMMA descriptor whose start address
+// is advanced by j*d rows (j*d*128 bytes).  The swizzle XOR is a function of absolute smem address bits, so the
+// row-shifted descriptor reads the row-shifted operand (verified on B200, profiles/r01_probe_umma_row_shift.log).
+//
+// A transposed convolution is the same kernel: phase r of the stride-u output is an ordinary 2-tap conv (K/u taps)
+// whose output "channels" are n = r*Cout + co of a [B, Tin, u*Cout] tensor -- which is bit-for-bit the
+// [B, u*Tin, Cout] result.  Each N tile lies inside one phase and uses that phase's tap base, so no zero-stuffed
+// tensor and no wasted MACs.
+//
+// Warp-specialised persistent CTAs (1 per SM):  warp 0 = TMA producer, warp 1 = UMMA issuer (+ TMEM allocator),
+// warps 2..5 = epilogue (tcgen05.ld -> +bias +residual, *scale, +accum -> fp32 and/or bf16 global stores).
+// Pipelines: A ring (one halo tile per K-block), B ring (one weight tile per K-block x tap), two TMEM accumulators
+// so the epilogue of tile i overlaps the MMAs of tile i+1.
+#include "bvg_common.cuh"
+#include "sm100_ptx.cuh"
+
+namespace bvg {
+
+constexpr int UMMA_BLOCK_M = 128;
+constexpr int UMMA_BLOCK_K = 64;  // bf16 elements per 128-byte swizzled row
+constexpr int UMMA_THREADS = 192;
+constexpr int UMMA_MAX_STAGES = 8;
+
+struct ConvUmmaParams {
+    const float* bias;      // [cout_phase] or null
+    const float* residual;  // [B,T,N] fp32 or null
+    const float* accum;     // [B,T,N] fp32 or null
+    float* y_f32;           // [B,T,N] or null
+    __nv_bfloat16* y_bf16;  // [B,T,N] or null
+    int64_t T;              // rows per batch item
+    int B;
+    int Cin;
+    int N;           // total output channels (u*Cout for a transposed conv)
+    int cout_phase;  // channels per phase (= N for a plain conv)
+    int taps;        // taps per phase
+    int dil;
+    int tap_base[BVG_MAX_PHASES];  // input row offset of tap 0 for each phase
+    int n_tile;                    // UMMA N (multiple of 16, <= 256)
+    int tiles_per_phase;           // ceil(cout_phase / n_tile)
+    int num_phases;
+    int64_t m_tiles;  // ceil(T / 128)
+    int64_t total_tiles;
+    int a_rows;      // rows of the A halo tile = 128 + (taps-1)*dil rounded up to 8
+    int a_stages, b_stages;
+    uint32_t a_stage_bytes, b_stage_bytes;
+    uint32_t tmem_cols;
+    float out_scale;
+};
+
+// smem carve-up: [A ring][B ring][barriers][tmem ptr]
+struct SmemLayout {
+    uint32_t a_off, b_off, bar_off, total;
+};
+static inline SmemLayout smem_layout(const ConvUmmaParams& p) {
+    SmemLayout l;
+    l.a_off = 0;
+    l.b_off = p.a_stages * p.a_stage_bytes;
+    l.bar_off = l.b_off + p.b_stages * p.b_stage_bytes;
+    l.total = l.bar_off + (2 * UMMA_MAX_STAGES * 2 + 4) * 8 + 16;
+    return l;
+}
+
+__global__ void __launch_bounds__(UMMA_THREADS, 1)
+conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_w,
+                 const __grid_constant__ ConvUmmaParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* sA = smem;
+    uint8_t* sB = smem + p.a_stages * p.a_stage_bytes;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sB + p.b_stages * p.b_stage_bytes);
+    uint64_t* a_full = bars;
+    uint64_t* a_empty = bars + UMMA_MAX_STAGES;
+    uint64_t* b_full = bars + 2 * UMMA_MAX_STAGES;
+    uint64_t* b_empty = bars + 3 * UMMA_MAX_STAGES;
+    uint64_t* acc_full = bars + 4 * UMMA_MAX_STAGES;   // [2]
+    uint64_t* acc_empty = acc_full + 2;                // [2]
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(acc_empty + 2);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+
+    if (threadIdx.x == 0) {
+        tma_prefetch_desc(&map_x);
+        tma_prefetch_desc(&map_w);
+        for (int i = 0; i < p.a_stages; ++i) { mbar_init(&a_full[i], 1); mbar_init(&a_empty[i], 1); }
+        for (int i = 0; i < p.b_stages; ++i) { mbar_init(&b_full[i], 1); mbar_init(&b_empty[i], 1); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 4); }
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc(tmem_ptr, p.tmem_cols);
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    const uint32_t tmem_base = *tmem_ptr;
+
+    const int k_blocks = (p.Cin + UMMA_BLOCK_K - 1) / UMMA_BLOCK_K;
+    const int n_tiles = p.num_phases * p.tiles_per_phase;
+
+    if (warp == 0) {
+        // ------------------------------ TMA producer ------------------------------
+        if (lane == 0) {
+            int sa = 0, sb = 0;
+            uint32_t pa = 0, pb = 0;
+            for (int64_t tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+                const int nt = static_cast<int>(tile % n_tiles);
+                const int64_t rest = tile / n_tiles;
+                const int64_t mt = rest % p.m_tiles;
+                const int b = static_cast<int>(rest / p.m_tiles);
+                const int phase = nt / p.tiles_per_phase;
+                const int n0 = phase * p.cout_phase + (nt % p.tiles_per_phase) * p.n_tile;
+                const int row0 = static_cast<int>(mt * UMMA_BLOCK_M) + p.tap_base[phase];
+                for (int kb = 0; kb < k_blocks; ++kb) {
+                    mbar_wait(&a_empty[sa], pa ^ 1);
+                    mbar_arrive_expect_tx(&a_full[sa], p.a_stage_bytes);
+                    tma_load_3d(sA + sa * p.a_stage_bytes, &map_x, &a_full[sa], kb * UMMA_BLOCK_K, row0, b);
+                    if (++sa == p.a_stages) { sa = 0; pa ^= 1; }
+                    for (int j = 0; j < p.taps; ++j) {
+                        mbar_wait(&b_empty[sb], pb ^ 1);
+                        mbar_arrive_expect_tx(&b_full[sb], p.b_stage_bytes);
+                        tma_load_3d_hint(sB + sb * p.b_stage_bytes, &map_w, &b_full[sb], kb * UMMA_BLOCK_K, n0, j,
+                                         kPolicyEvictLast);
+                        if (++sb == p.b_stages) { sb = 0; pb ^= 1; }
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ------------------------------ UMMA issuer ------------------------------
+        if (lane == 0) {
+            const uint32_t idesc = umma_idesc_bf16_f32(UMMA_BLOCK_M, p.n_tile);
+            int sa = 0, sb = 0, acc = 0;
+            uint32_t pa = 0, pb = 0, pacc = 0;
+            for (int64_t tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+                mbar_wait(&acc_empty[acc], pacc ^ 1);
+                tc_fence_after_sync();
+                const uint32_t d_tmem = tmem_base + acc * p.n_tile;
+                uint32_t accumulate = 0;
+                for (int kb = 0; kb < k_blocks; ++kb) {
+                    const int k_rem = p.Cin - kb * UMMA_BLOCK_K;
+                    const int k_steps = (min(k_rem, UMMA_BLOCK_K) + 15) / 16;
+                    mbar_wait(&a_full[sa], pa);
+                    const uint32_t a_addr = smem_u32(sA + sa * p.a_stage_bytes);
+                    for (int j = 0; j < p.taps; ++j) {
+                        mbar_wait(&b_full[sb], pb);
+                        tc_fence_after_sync();
+                        const uint32_t b_addr = smem_u32(sB + sb * p.b_stage_bytes);
+                        const uint32_t a_tap = a_addr + static_cast<uint32_t>(j * p.dil) * 128u;
+                        for (int ks = 0; ks < k_steps; ++ks) {
+                            umma_f16(d_tmem, umma_desc_sw128_kmajor(a_tap + ks * 32), umma_desc_sw128_kmajor(b_addr + ks * 32),
+                                     idesc, accumulate);
+                            accumulate = 1;
+                        }
+                        umma_commit(&b_empty[sb]);
+                        if (++sb == p.b_stages) { sb = 0; pb ^= 1; }
+                    }
+                    umma_commit(&a_empty[sa]);
+                    if (++sa == p.a_stages) { sa = 0; pa ^= 1; }
+                }
+                umma_commit(&acc_full[acc]);
+                if (++acc == 2) { acc = 0; pacc ^= 1; }
+            }
+        }
+    } else {
+        // ------------------------------ epilogue (warps 2..5) ------------------------------
+        const int q = warp & 3;  // TMEM lane quarter this warp may access
+        int acc = 0;
+        uint32_t pacc = 0;
+        for (int64_t tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+            const int nt = static_cast<int>(tile % n_tiles);
+            const int64_t rest = tile / n_tiles;
+            const int64_t mt = rest % p.m_tiles;
+            const int64_t b = rest / p.m_tiles;
+            const int phase = nt / p.tiles_per_phase;
+            const int c0 = (nt % p.tiles_per_phase) * p.n_tile;  // channel offset inside the phase
+            const int c_end = p.cout_phase;                      // valid channels of this phase
+            const int64_t t = mt * UMMA_BLOCK_M + q * 32 + lane;
+            const bool row_ok = t < p.T;
+            const int64_t row_off = (b * p.T + t) * p.N + phase * p.cout_phase;
+
+            mbar_wait(&acc_full[acc], pacc);
+            tc_fence_after_sync();
+            const uint32_t t_addr = tmem_base + ((static_cast<uint32_t>(q) * 32u) << 16) + acc * p.n_tile;
+            for (int c = 0; c < p.n_tile; c += 16) {
+                uint32_t v[16];
+                tmem_ld_32x32b_x16(t_addr + c, v);  // warp-collective: executed by all lanes
+                tmem_ld_wait();
+                if (row_ok) {
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        const int ch = c0 + c + 8 * h;
+                        if (ch < c_end) {  // channel counts are multiples of 8
+                            float o[8];
+#pragma unroll
+                            for (int e = 0; e < 8; ++e) o[e] = __uint_as_float(v[8 * h + e]);
+                            if (p.bias) {
+                                const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.bias + ch));
+                                const float4 b1 = __ldg(reinterpret_cast<const float4*>(p.bias + ch + 4));
+                                o[0] += b0.x; o[1] += b0.y; o[2] += b0.z; o[3] += b0.w;
+                                o[4] += b1.x; o[5] += b1.y; o[6] += b1.z; o[7] += b1.w;
+                            }
+                            if (p.residual) {
+                                const float4 r0 = *reinterpret_cast<const float4*>(p.residual + row_off + ch);
+                                const float4 r1 = *reinterpret_cast<const float4*>(p.residual + row_off + ch + 4);
+                                o[0] += r0.x; o[1] += r0.y; o[2] += r0.z; o[3] += r0.w;
+                                o[4] += r1.x; o[5] += r1.y; o[6] += r1.z; o[7] += r1.w;
+                            }
+#pragma unroll
+                            for (int e = 0; e < 8; ++e) o[e] *= p.out_scale;
+                            if (p.accum) {
+                                const float4 r0 = *reinterpret_cast<const float4*>(p.accum + row_off + ch);
+                                const float4 r1 = *reinterpret_cast<const float4*>(p.accum + row_off + ch + 4);
+                                o[0] += r0.x; o[1] += r0.y; o[2] += r0.z; o[3] += r0.w;
+                                o[4] += r1.x; o[5] += r1.y; o[6] += r1.z; o[7] += r1.w;
+                            }
+                            if (p.y_f32) {
+                                *reinterpret_cast<float4*>(p.y_f32 + row_off + ch) = make_float4(o[0], o[1], o[2], o[3]);
+                                *reinterpret_cast<float4*>(p.y_f32 + row_off + ch + 4) = make_float4(o[4], o[5], o[6], o[7]);
+                            }
+                            if (p.y_bf16) {
+                                __nv_bfloat162 h0 = __floats2bfloat162_rn(o[0], o[1]);
+                                __nv_bfloat162 h1 = __floats2bfloat162_rn(o[2], o[3]);
+                                __nv_bfloat162 h2 = __floats2bfloat162_rn(o[4], o[5]);
+                                __nv_bfloat162 h3 = __floats2bfloat162_rn(o[6], o[7]);
+                                *reinterpret_cast<uint4*>(p.y_bf16 + row_off + ch) =
+                                    make_uint4(*reinterpret_cast<unsigned int*>(&h0), *reinterpret_cast<unsigned int*>(&h1),
+                                               *reinterpret_cast<unsigned int*>(&h2), *reinterpret_cast<unsigned int*>(&h3));
+                            }
+                        }
+                    }
+                }
+            }
+            tc_fence_before_sync();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&acc_empty[acc]);
+            if (++acc == 2) { acc = 0; pacc ^= 1; }
+        }
+    }
+
+    tc_fence_before_sync();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after_sync();
+        tmem_dealloc(tmem_base, p.tmem_cols);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+    static EncodeTiledFn fn = []() -> EncodeTiledFn {
+        void* f = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) != cudaSuccess) return nullptr;
+        return reinterpret_cast<EncodeTiledFn>(f);
+    }();
+    return fn;
+}
+
+static int device_sm_count() {
+    static thread_local int cached_dev = -1, cached = 0;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev != cached_dev) {
+        cudaDeviceGetAttribute(&cached, cudaDevAttrMultiProcessorCount, dev);
+        cached_dev = dev;
+    }
+    return cached;
+}
+
+static int encode_3d_bf16(CUtensorMap* map, const void* ptr, uint64_t d0, uint64_t d1, uint64_t d2, uint32_t b0,
+                          uint32_t b1, uint32_t b2, const char* what) {
+    EncodeTiledFn enc = get_encode_fn();
+    BVG_REQUIRE(enc != nullptr, BVG_ERR_CUDA, "cuTensorMapEncodeTiled not available from the driver");
+    cuuint64_t dims[3] = {d0, d1, d2};
+    cuuint64_t strides[2] = {d0 * 2, d0 * d1 * 2};
+    cuuint32_t box[3] = {b0, b1, b2};
+    cuuint32_t es[3] = {1, 1, 1};
+    CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(ptr), dims, strides, box, es,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    BVG_REQUIRE(r == CUDA_SUCCESS, BVG_ERR_CUDA,
+                "cuTensorMapEncodeTiled(%s) failed with CUresult %d (dims %llu x %llu x %llu, box %u x %u x %u)", what,
+                (int)r, (unsigned long long)d0, (unsigned long long)d1, (unsigned long long)d2, b0, b1, b2);
+    return BVG_OK;
+}
+
+// Generic launcher: plain conv (num_phases = 1) or polyphase transposed conv.
+int conv_umma_launch(const void* x, const void* w_packed, const float* bias, const float* residual, const float* accum,
+                     float* y_f32, void* y_bf16, int64_t B, int64_t T, int64_t Cin, int64_t N, int64_t cout_phase,
+                     int taps, int dil, const int* tap_base, int num_phases, float out_scale, cudaStream_t st) {
+    BVG_REQUIRE(x && w_packed && (y_f32 || y_bf16), BVG_ERR_INVALID, "conv_umma: null pointer");
+    BVG_REQUIRE(Cin % 8 == 0 && cout_phase % 8 == 0 && N == cout_phase * num_phases, BVG_ERR_UNSUPPORTED,
+                "conv_umma: Cin=%lld and Cout=%lld must be multiples of 8", (long long)Cin, (long long)cout_phase);
+    BVG_REQUIRE(taps >= 1 && taps <= 11 && dil >= 1 && (taps - 1) * dil <= 120, BVG_ERR_UNSUPPORTED,
+                "conv_umma: taps=%d dilation=%d outside the supported range", taps, dil);
+    BVG_REQUIRE(num_phases >= 1 && num_phases <= BVG_MAX_PHASES, BVG_ERR_UNSUPPORTED, "conv_umma: %d phases", num_phases);
+    BVG_REQUIRE(T < (int64_t(1) << 31) - 256 && B < 65536, BVG_ERR_UNSUPPORTED, "conv_umma: T or B too large");
+    BVG_REQUIRE((reinterpret_cast<uintptr_t>(x) % 16 == 0) && (reinterpret_cast<uintptr_t>(w_packed) % 16 == 0),
+                BVG_ERR_INVALID, "conv_umma: x / w must be 16-byte aligned");
+    if (B == 0 || T == 0) return BVG_OK;
+
+    ConvUmmaParams p{};
+    p.bias = bias; p.residual = residual; p.accum = accum; p.y_f32 = y_f32;
+    p.y_bf16 = static_cast<__nv_bfloat16*>(y_bf16);
+    p.T = T; p.B = (int)B; p.Cin = (int)Cin; p.N = (int)N; p.cout_phase = (int)cout_phase;
+    p.taps = taps; p.dil = dil; p.num_phases = num_phases; p.out_scale = out_scale;
+    for (int r = 0; r < num_phases; ++r) p.tap_base[r] = tap_base[r];
+    // N tile: cover a phase with as few equal tiles as possible, <= 256 wide, multiple of 16
+    {
+        const int cp = (int)cout_phase;
+        int nt = (cp + 255) / 256;
+        int tile = (int)round_up(ceil_div(cp, nt), 16);
+        p.n_tile = tile;
+        p.tiles_per_phase = (int)ceil_div(cp, tile);
+    }
+    p.m_tiles = ceil_div(T, UMMA_BLOCK_M);
+    p.total_tiles = p.m_tiles * B * p.num_phases * p.tiles_per_phase;
+    p.a_rows = (int)round_up(UMMA_BLOCK_M + (taps - 1) * dil, 8);
+    p.a_stage_bytes = (uint32_t)round_up((int64_t)p.a_rows * 128, 1024);
+    p.b_stage_bytes = (uint32_t)round_up((int64_t)p.n_tile * 128, 1024);
+    uint32_t tm = 32;
+    while (tm < (uint32_t)(2 * p.n_tile)) tm <<= 1;
+    p.tmem_cols = tm;
+    // stages: fill ~200 KB; at least 2 A stages, B stages up to 8
+    const uint32_t budget = 200 * 1024;
+    p.a_stages = 2;
+    int bs = (int)((budget - p.a_stages * p.a_stage_bytes) / p.b_stage_bytes);
+    if (bs > UMMA_MAX_STAGES) bs = UMMA_MAX_STAGES;
+    BVG_REQUIRE(bs >= 2, BVG_ERR_UNSUPPORTED, "conv_umma: tile does not fit shared memory");
+    p.b_stages = bs;
+    if ((uint32_t)(3 * p.a_stage_bytes + p.b_stages * p.b_stage_bytes) <= budget) p.a_stages = 3;
+    const SmemLayout lay = smem_layout(p);
+    const uint32_t smem_bytes = lay.total + 1024;
+
+    CUtensorMap map_x, map_w;
+    // the A box is a_stage_bytes/128 rows so that expect_tx matches the bytes TMA writes
+    const uint32_t a_box_rows = p.a_stage_bytes / 128;
+    BVG_REQUIRE(a_box_rows <= 256, BVG_ERR_UNSUPPORTED, "conv_umma: halo tile of %u rows exceeds the TMA box limit", a_box_rows);
+    int rc = encode_3d_bf16(&map_x, x, (uint64_t)Cin, (uint64_t)T, (uint64_t)B, UMMA_BLOCK_K, a_box_rows, 1, "x");
+    if (rc != BVG_OK) return rc;
+    const uint32_t b_box_rows = p.b_stage_bytes / 128;
+    rc = encode_3d_bf16(&map_w, w_packed, (uint64_t)Cin, (uint64_t)N, (uint64_t)taps, UMMA_BLOCK_K, b_box_rows, 1, "w");
+    if (rc != BVG_OK) return rc;
+
+    {   // opt in to the large dynamic shared memory carve-out once per device
+        static bool attr_set[64] = {};
+        int dev = 0;
+        BVG_CUDA(cudaGetDevice(&dev));
+        if (dev < 0 || dev >= 64 || !attr_set[dev]) {
+            BVG_CUDA(cudaFuncSetAttribute(conv_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+            if (dev >= 0 && dev < 64) attr_set[dev] = true;
+        }
+    }
+    const int sms = device_sm_count();
+    const int grid = (int)(p.total_tiles < sms ? p.total_tiles : sms);
+    conv_umma_kernel<<<grid, UMMA_THREADS, smem_bytes, st>>>(map_x, map_w, p);
+    BVG_LAUNCH_CHECK("conv_umma_kernel");
+    return BVG_OK;
+}
+
+}  // namespace bvg

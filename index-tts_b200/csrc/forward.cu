@@ -1,0 +1,207 @@
+// C-ABI entry points for the convolutions and the whole-generator launch plan (reference bigvgan.py:360-386).
+#include "bvg_common.cuh"
+
+namespace bvg {
+int conv_umma_launch(const void* x, const void* w_packed, const float* bias, const float* residual, const float* accum,
+                     float* y_f32, void* y_bf16, int64_t B, int64_t T, int64_t Cin, int64_t N, int64_t cout_phase,
+                     int taps, int dil, const int* tap_base, int num_phases, float out_scale, cudaStream_t st);
+int conv_simt_launch(const void* x, const void* w_packed, const float* bias, const float* residual, const float* accum,
+                     float* y_f32, void* y_bf16, int64_t B, int64_t T, int64_t Cin, int64_t N, int64_t cout_phase,
+                     int taps, int dil, const int* tap_base, int num_phases, float out_scale, cudaStream_t st);
+int activation1d_nlc(const void* x, int x_dtype, void* y, int y_dtype, const float* alpha, const float* beta,
+                     int64_t B, int64_t T, int64_t C, int precise, cudaStream_t st);
+int transpose_any(const void* src, int src_dtype, void* dst, int dst_dtype, int64_t B, int64_t R, int64_t Cc, int64_t sb,
+                  int64_t sr, cudaStream_t st);
+
+static int conv_dispatch(int precision, const void* x, const void* w, const float* bias, const float* residual,
+                         const float* accum, float* y_f32, void* y_bf16, int64_t B, int64_t T, int64_t Cin, int64_t N,
+                         int64_t cout_phase, int taps, int dil, const int* tap_base, int num_phases, float out_scale,
+                         cudaStream_t st) {
+    if (precision == BVG_BF16_TC)
+        return conv_umma_launch(x, w, bias, residual, accum, y_f32, y_bf16, B, T, Cin, N, cout_phase, taps, dil, tap_base,
+                                num_phases, out_scale, st);
+    if (precision == BVG_EXACT_F32)
+        return conv_simt_launch(x, w, bias, residual, accum, y_f32, y_bf16, B, T, Cin, N, cout_phase, taps, dil, tap_base,
+                                num_phases, out_scale, st);
+    return set_error(BVG_ERR_UNSUPPORTED, "unknown precision mode %d", precision);
+}
+
+static int conv1d(int precision, const void* x, const void* w, const float* bias, const float* residual,
+                  const float* accum, float* y_f32, void* y_bf16, int64_t B, int64_t T, int64_t Cin, int64_t Cout, int k,
+                  int dil, float out_scale, cudaStream_t st) {
+    BVG_REQUIRE(k % 2 == 1, BVG_ERR_UNSUPPORTED, "conv1d: kernel size %d must be odd ('same' padding)", k);
+    const int base = -((k - 1) / 2) * dil;
+    return conv_dispatch(precision, x, w, bias, residual, accum, y_f32, y_bf16, B, T, Cin, Cout, Cout, k, dil, &base, 1,
+                         out_scale, st);
+}
+
+static int convtranspose1d(int precision, const void* x, const void* w, const float* bias, float* y_f32, void* y_bf16,
+                           int64_t B, int64_t Tin, int64_t Cin, int64_t Cout, int K, int u, cudaStream_t st) {
+    BVG_REQUIRE(u >= 1 && u <= BVG_MAX_PHASES && K % u == 0 && (K - u) % 2 == 0, BVG_ERR_UNSUPPORTED,
+                "convtranspose1d: need K %% u == 0, (K-u) even, u <= %d (got K=%d u=%d)", BVG_MAX_PHASES, K, u);
+    const int taps = K / u, p = (K - u) / 2;
+    int base[BVG_MAX_PHASES];
+    for (int r = 0; r < u; ++r) base[r] = (r + p) / u - (taps - 1);
+    return conv_dispatch(precision, x, w, bias, nullptr, nullptr, y_f32, y_bf16, B, Tin, Cin, (int64_t)u * Cout, Cout, taps,
+                         1, base, u, 1.0f, st);
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// whole generator
+// ------------------------------------------------------------------------------------------------------------
+struct Plan {
+    int64_t B, T_mel, E;  // E = max over stages of B*T_i*C_i
+    size_t op_es;         // bytes per MMA-operand element
+    size_t off_mel, off_pre, off_x, off_r, off_a, off_y1, off_sum, off_sumop, total;
+};
+
+static size_t align256(size_t v) { return (v + 255) & ~size_t(255); }
+
+static int make_plan(const bvg_model_desc* m, int64_t B, int64_t T_mel, Plan* pl) {
+    BVG_REQUIRE(m != nullptr, BVG_ERR_INVALID, "null model descriptor");
+    BVG_REQUIRE(m->num_stages >= 1 && m->num_stages <= BVG_MAX_STAGES && m->num_kernels >= 1 &&
+                    m->num_kernels <= BVG_MAX_KERNELS && m->num_dilations >= 1 && m->num_dilations <= BVG_MAX_DILATIONS,
+                BVG_ERR_UNSUPPORTED, "model descriptor: stages/kernels/dilations out of range");
+    BVG_REQUIRE(m->precision == BVG_EXACT_F32 || m->precision == BVG_BF16_TC, BVG_ERR_UNSUPPORTED,
+                "model descriptor: unknown precision %d", m->precision);
+    BVG_REQUIRE(m->num_mels % 8 == 0 && (m->upsample_initial_channel >> m->num_stages) % 8 == 0, BVG_ERR_UNSUPPORTED,
+                "channel counts must be multiples of 8 (num_mels=%d, last stage %d)", m->num_mels,
+                m->upsample_initial_channel >> m->num_stages);
+    pl->B = B;
+    pl->T_mel = T_mel;
+    pl->op_es = m->precision == BVG_BF16_TC ? 2 : 4;
+    int64_t T = T_mel, E = 0;
+    for (int i = 0; i < m->num_stages; ++i) {
+        T *= m->upsample_rates[i];
+        const int64_t C = m->upsample_initial_channel >> (i + 1);
+        E = E > B * T * C ? E : B * T * C;
+    }
+    pl->E = E;
+    size_t o = 0;
+    pl->off_mel = o;   o += align256((size_t)B * T_mel * m->num_mels * pl->op_es);
+    pl->off_pre = o;   o += align256((size_t)B * T_mel * m->upsample_initial_channel * pl->op_es);
+    pl->off_x = o;     o += align256((size_t)E * 4);
+    pl->off_r = o;     o += align256((size_t)E * 4);
+    pl->off_a = o;     o += align256((size_t)E * pl->op_es);
+    pl->off_y1 = o;    o += align256((size_t)E * 4);
+    pl->off_sum = o;   o += align256((size_t)E * 4);
+    pl->off_sumop = o; o += align256((size_t)E * pl->op_es);
+    pl->total = o;
+    return BVG_OK;
+}
+
+}  // namespace bvg
+
+using namespace bvg;
+
+extern "C" int bvg_conv1d_nlc_fwd(const void* x, const void* w_packed, const float* bias, const float* residual,
+                                  const float* accum, float* y_f32, void* y_bf16, int64_t B, int64_t T, int64_t Cin,
+                                  int64_t Cout, int k, int dilation, float out_scale, int precision, void* stream) {
+    return conv1d(precision, x, w_packed, bias, residual, accum, y_f32, y_bf16, B, T, Cin, Cout, k, dilation, out_scale,
+                  static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int bvg_convtranspose1d_nlc_fwd(const void* x, const void* w_packed, const float* bias, float* y_f32,
+                                           void* y_bf16, int64_t B, int64_t Tin, int64_t Cin, int64_t Cout, int K, int u,
+                                           int precision, void* stream) {
+    return convtranspose1d(precision, x, w_packed, bias, y_f32, y_bf16, B, Tin, Cin, Cout, K, u,
+                           static_cast<cudaStream_t>(stream));
+}
+
+extern "C" size_t bvg_workspace_bytes(const bvg_model_desc* m, int64_t B, int64_t T_mel) {
+    Plan pl;
+    if (B <= 0 || T_mel <= 0) return 256;
+    if (make_plan(m, B, T_mel, &pl) != BVG_OK) return 0;
+    return pl.total + 256;
+}
+
+extern "C" int bvg_forward(const bvg_model_desc* m, const float* mel, int64_t mel_stride_b, int64_t mel_stride_c,
+                           float* wav, int64_t B, int64_t T_mel, void* workspace, size_t workspace_bytes, void* stream) {
+    BVG_REQUIRE(m && mel && wav, BVG_ERR_INVALID, "bvg_forward: null pointer");
+    BVG_REQUIRE(B >= 0 && T_mel >= 0, BVG_ERR_INVALID, "bvg_forward: negative shape");
+    if (B == 0 || T_mel == 0) return BVG_OK;
+    Plan pl;
+    int rc = make_plan(m, B, T_mel, &pl);
+    if (rc != BVG_OK) return rc;
+    BVG_REQUIRE(workspace != nullptr && workspace_bytes >= pl.total, BVG_ERR_WORKSPACE,
+                "bvg_forward: workspace of %zu bytes is smaller than the %zu required", workspace_bytes, pl.total);
+    BVG_REQUIRE(reinterpret_cast<uintptr_t>(workspace) % 256 == 0, BVG_ERR_INVALID, "bvg_forward: workspace must be 256-byte aligned");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int prec = m->precision;
+    const bool tc = prec == BVG_BF16_TC;
+    const int op_dt = tc ? BVG_BF16 : BVG_F32;
+    const int precise = tc ? 0 : 1;
+    uint8_t* ws = static_cast<uint8_t*>(workspace);
+    void* mel_nlc = ws + pl.off_mel;
+    void* pre = ws + pl.off_pre;
+    float* X = reinterpret_cast<float*>(ws + pl.off_x);
+    float* R = reinterpret_cast<float*>(ws + pl.off_r);
+    void* A = ws + pl.off_a;
+    void* Y1 = ws + pl.off_y1;
+    float* SUM = reinterpret_cast<float*>(ws + pl.off_sum);
+    void* SUMOP = ws + pl.off_sumop;
+
+    // mel [B, num_mels, T] -> [B, T, num_mels] in the operand dtype
+    rc = transpose_any(mel, BVG_F32, mel_nlc, op_dt, B, m->num_mels, T_mel, mel_stride_b, mel_stride_c, st);
+    if (rc != BVG_OK) return rc;
+    // conv_pre (bigvgan.py:362): output feeds the first transposed conv directly -> operand dtype
+    {
+        const bvg_conv_desc& c = m->conv_pre;
+        rc = conv1d(prec, mel_nlc, c.w, c.bias, nullptr, nullptr, tc ? nullptr : reinterpret_cast<float*>(pre),
+                    tc ? pre : nullptr, B, T_mel, c.cin, c.cout, c.k, 1, 1.0f, st);
+        if (rc != BVG_OK) return rc;
+    }
+    const void* stage_in = pre;
+    int64_t T = T_mel;
+    int C = m->upsample_initial_channel;
+    const float inv_nk = 1.0f / static_cast<float>(m->num_kernels);
+    for (int i = 0; i < m->num_stages; ++i) {
+        const bvg_conv_desc& up = m->ups[i];
+        const int u = m->upsample_rates[i];
+        BVG_REQUIRE(up.cin == C && up.cout == C / 2, BVG_ERR_INVALID, "ups[%d]: channel mismatch", i);
+        // upsample (bigvgan.py:366-367): fp32 residual stream X
+        rc = convtranspose1d(prec, stage_in, up.w, up.bias, X, nullptr, B, T, C, C / 2, up.k, u, st);
+        if (rc != BVG_OK) return rc;
+        T *= u;
+        C /= 2;
+        const bool last_stage = (i + 1 == m->num_stages);
+        for (int j = 0; j < m->num_kernels; ++j) {
+            const float* xr = X;  // residual stream of this block (bigvgan.py:132-141)
+            for (int l = 0; l < m->num_dilations; ++l) {
+                const bvg_conv_desc& c1 = m->convs1[i][j][l];
+                const bvg_conv_desc& c2 = m->convs2[i][j][l];
+                const bvg_act_desc& a1 = m->acts[i][j][2 * l];
+                const bvg_act_desc& a2 = m->acts[i][j][2 * l + 1];
+                rc = activation1d_nlc(xr, BVG_F32, A, op_dt, a1.alpha_log, a1.beta_log, B, T, C, precise, st);
+                if (rc != BVG_OK) return rc;
+                // xt between c1 and a2 is an intermediate (not the residual stream): operand dtype (bf16 in TC mode;
+                // costs ~1.2 dB of the 43.8 dB budget, tools/emulate_bf16_plan.py)
+                rc = conv1d(prec, A, c1.w, c1.bias, nullptr, nullptr, tc ? nullptr : reinterpret_cast<float*>(Y1),
+                            tc ? Y1 : nullptr, B, T, C, C, c1.k, c1.dilation, 1.0f, st);
+                if (rc != BVG_OK) return rc;
+                rc = activation1d_nlc(Y1, op_dt, A, op_dt, a2.alpha_log, a2.beta_log, B, T, C, precise, st);
+                if (rc != BVG_OK) return rc;
+                const bool last = (l + 1 == m->num_dilations);
+                if (!last) {
+                    // x = xt + x
+                    rc = conv1d(prec, A, c2.w, c2.bias, xr, nullptr, R, nullptr, B, T, C, C, c2.k, 1, 1.0f, st);
+                    xr = R;
+                } else {
+                    // xs (+)= block output; x = xs / num_kernels (bigvgan.py:369-375) folded into the epilogue.
+                    // The last block of a stage also emits the operand-dtype copy the next transposed conv reads.
+                    const bool emit_op = tc && !last_stage && (j + 1 == m->num_kernels);
+                    rc = conv1d(prec, A, c2.w, c2.bias, xr, j > 0 ? SUM : nullptr, SUM, emit_op ? SUMOP : nullptr, B, T, C, C,
+                                c2.k, 1, inv_nk, st);
+                }
+                if (rc != BVG_OK) return rc;
+            }
+        }
+        stage_in = tc ? SUMOP : static_cast<const void*>(SUM);
+    }
+    // activation_post -> conv_post -> clamp / tanh (bigvgan.py:378-384), fp32 in both modes
+    rc = activation1d_nlc(SUM, BVG_F32, R, BVG_F32, m->act_post.alpha_log, m->act_post.beta_log, B, T, C, precise, st);
+    if (rc != BVG_OK) return rc;
+    const bvg_conv_desc& cp = m->conv_post;
+    BVG_REQUIRE(cp.cout == 1 && cp.cin == C, BVG_ERR_UNSUPPORTED, "conv_post must map %d channels to 1", C);
+    return bvg_conv_post_fwd(R, static_cast<const float*>(cp.w), cp.bias, wav, B, T, C, cp.k, m->use_tanh_at_final, stream);
+}

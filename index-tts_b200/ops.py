@@ -1,0 +1,228 @@
+"""Torch-facing wrappers over the C ABI (``include/bvg.h``).
+
+Torch is plumbing here: it owns device memory and the current stream; every computation is a call into
+``libbvg.so`` through ctypes.  The ops are also registered with ``torch.library`` (namespace ``bvg``) with fake
+(meta) implementations so that ``torch.compile(dynamic=True)`` (reference infer_v2.py:267-270) can trace through
+the module.  There is no autograd formula (the reference extension raises in backward, activation1d.py:29-32)
+and no CPU implementation: a non-CUDA tensor is an error.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+
+from . import _lib
+from ._lib import BVG_BF16, BVG_BF16_TC, BVG_EXACT_F32, BVG_F32, check
+
+_DT = {torch.float32: BVG_F32, torch.bfloat16: BVG_BF16}
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def _require_cuda(t: torch.Tensor, what: str):
+    if not t.is_cuda:
+        raise _lib.BvgError(f"{what}: expected a CUDA tensor, got device {t.device} (libbvg has no CPU path)")
+    _lib.require_device(t.device.index if t.device.index is not None else torch.cuda.current_device())
+
+
+def _dt(t: torch.Tensor, what: str) -> int:
+    if t.dtype not in _DT:
+        raise _lib.BvgError(f"{what}: dtype {t.dtype} not supported (float32 and bfloat16 only)")
+    return _DT[t.dtype]
+
+
+def precision_code(name) -> int:
+    if name in (BVG_EXACT_F32, "fp32", "float32", "exact", torch.float32):
+        return BVG_EXACT_F32
+    if name in (BVG_BF16_TC, "bf16", "bfloat16", torch.bfloat16):
+        return BVG_BF16_TC
+    raise ValueError(f"unknown precision {name!r} (use 'bf16' or 'fp32')")
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# Activation1d
+# ---------------------------------------------------------------------------------------------------------------
+def _activation1d_impl(x: torch.Tensor, alpha_log: torch.Tensor, beta_log: torch.Tensor, precise: bool) -> torch.Tensor:
+    _require_cuda(x, "activation1d")
+    if x.dim() != 3:
+        raise _lib.BvgError(f"activation1d: expected [B, C, T], got shape {tuple(x.shape)}")
+    dt = _dt(x, "activation1d")
+    B, C, T = x.shape
+    if T > 0 and x.stride(2) != 1:
+        x = x.contiguous()
+    y = torch.empty((B, C, T), dtype=x.dtype, device=x.device)
+    if B * C * T == 0:
+        return y
+    a = alpha_log.detach().to(device=x.device, dtype=torch.float32).contiguous()
+    b = beta_log.detach().to(device=x.device, dtype=torch.float32).contiguous()
+    if a.numel() != C or b.numel() != C:
+        raise _lib.BvgError(f"activation1d: alpha/beta must have {C} elements")
+    with torch.cuda.device(x.device):
+        check(_lib.load().bvg_activation1d_fwd(x.data_ptr(), y.data_ptr(), a.data_ptr(), b.data_ptr(), B, C, T,
+                                               x.stride(0), x.stride(1), dt, int(bool(precise)), _stream()),
+              "bvg_activation1d_fwd")
+    return y
+
+
+@torch.library.custom_op("bvg::activation1d", mutates_args=())
+def activation1d(x: torch.Tensor, alpha_log: torch.Tensor, beta_log: torch.Tensor, precise: bool) -> torch.Tensor:
+    """Fused up2 -> SnakeBeta -> down2 on ``[B, C, T]`` (same call shape as the reference's
+    ``anti_alias_activation_cuda.forward`` minus the constant filter arguments)."""
+    return _activation1d_impl(x, alpha_log, beta_log, precise)
+
+
+@activation1d.register_fake
+def _(x, alpha_log, beta_log, precise):
+    return torch.empty_like(x, memory_format=torch.contiguous_format)
+
+
+def activation1d_nlc(x: torch.Tensor, alpha_log: torch.Tensor, beta_log: torch.Tensor, out_dtype: torch.dtype,
+                     precise: bool) -> torch.Tensor:
+    """Channels-last ``[B, T, C]`` variant used inside the generator."""
+    _require_cuda(x, "activation1d_nlc")
+    x = x.contiguous()
+    B, T, C = x.shape
+    y = torch.empty((B, T, C), dtype=out_dtype, device=x.device)
+    with torch.cuda.device(x.device):
+        check(_lib.load().bvg_activation1d_nlc_fwd(x.data_ptr(), _dt(x, "activation1d_nlc"), y.data_ptr(), _DT[out_dtype],
+                                                   alpha_log.data_ptr(), beta_log.data_ptr(), B, T, C,
+                                                   int(bool(precise)), _stream()), "bvg_activation1d_nlc_fwd")
+    return y
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# layout + weights
+# ---------------------------------------------------------------------------------------------------------------
+def ncl_to_nlc(x: torch.Tensor, out_dtype: torch.dtype) -> torch.Tensor:
+    _require_cuda(x, "ncl_to_nlc")
+    if x.stride(2) != 1:
+        x = x.contiguous()
+    B, Cc, T = x.shape
+    y = torch.empty((B, T, Cc), dtype=out_dtype, device=x.device)
+    with torch.cuda.device(x.device):
+        check(_lib.load().bvg_ncl_to_nlc(x.data_ptr(), _dt(x, "ncl_to_nlc"), x.stride(0), x.stride(1), y.data_ptr(),
+                                         _DT[out_dtype], B, Cc, T, _stream()), "bvg_ncl_to_nlc")
+    return y
+
+
+def nlc_to_ncl(x: torch.Tensor, out_dtype: torch.dtype) -> torch.Tensor:
+    _require_cuda(x, "nlc_to_ncl")
+    x = x.contiguous()
+    B, T, Cc = x.shape
+    y = torch.empty((B, Cc, T), dtype=out_dtype, device=x.device)
+    with torch.cuda.device(x.device):
+        check(_lib.load().bvg_nlc_to_ncl(x.data_ptr(), _dt(x, "nlc_to_ncl"), y.data_ptr(), _DT[out_dtype], B, Cc, T,
+                                         _stream()), "bvg_nlc_to_ncl")
+    return y
+
+
+def fold_weight_norm(v: torch.Tensor, g: torch.Tensor) -> torch.Tensor:
+    """``g * v / ||v||`` over all dims but 0 (reference bigvgan.py:388-400 via torch's remove_weight_norm)."""
+    _require_cuda(v, "fold_weight_norm")
+    v = v.detach().float().contiguous()
+    g = g.detach().float().contiguous()
+    w = torch.empty_like(v)
+    rows = v.shape[0]
+    with torch.cuda.device(v.device):
+        check(_lib.load().bvg_fold_weight_norm(v.data_ptr(), g.data_ptr(), w.data_ptr(), rows, v.numel() // max(rows, 1),
+                                               _stream()), "bvg_fold_weight_norm")
+    return w
+
+
+def pack_conv1d_weight(w: torch.Tensor, precision: int) -> torch.Tensor:
+    """``[Cout, Cin, k]`` fp32 -> ``[k, Cout, Cin]`` in the operand dtype of ``precision``."""
+    _require_cuda(w, "pack_conv1d_weight")
+    w = w.detach().float().contiguous()
+    Cout, Cin, k = w.shape
+    dt = torch.bfloat16 if precision == BVG_BF16_TC else torch.float32
+    out = torch.empty((k, Cout, Cin), dtype=dt, device=w.device)
+    with torch.cuda.device(w.device):
+        check(_lib.load().bvg_pack_conv1d_weight(w.data_ptr(), out.data_ptr(), Cout, Cin, k, _DT[dt], _stream()),
+              "bvg_pack_conv1d_weight")
+    return out
+
+
+def pack_convtranspose1d_weight(w: torch.Tensor, stride: int, precision: int) -> torch.Tensor:
+    """``[Cin, Cout, K]`` fp32 -> polyphase ``[K/u, u*Cout, Cin]``."""
+    _require_cuda(w, "pack_convtranspose1d_weight")
+    w = w.detach().float().contiguous()
+    Cin, Cout, K = w.shape
+    dt = torch.bfloat16 if precision == BVG_BF16_TC else torch.float32
+    out = torch.empty((K // stride, stride * Cout, Cin), dtype=dt, device=w.device)
+    with torch.cuda.device(w.device):
+        check(_lib.load().bvg_pack_convtranspose1d_weight(w.data_ptr(), out.data_ptr(), Cin, Cout, K, stride, _DT[dt],
+                                                          _stream()), "bvg_pack_convtranspose1d_weight")
+    return out
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# convolutions (channels-last)
+# ---------------------------------------------------------------------------------------------------------------
+def conv1d_nlc(x: torch.Tensor, w_packed: torch.Tensor, bias: Optional[torch.Tensor], dilation: int, precision: int,
+               residual: Optional[torch.Tensor] = None, accum: Optional[torch.Tensor] = None, out_scale: float = 1.0,
+               out_f32: bool = True, out_bf16: bool = False):
+    _require_cuda(x, "conv1d_nlc")
+    x = x.contiguous()
+    B, T, Cin = x.shape
+    k, Cout, Cin2 = w_packed.shape
+    if Cin2 != Cin:
+        raise _lib.BvgError(f"conv1d_nlc: weight has {Cin2} input channels, x has {Cin}")
+    want = torch.bfloat16 if precision == BVG_BF16_TC else torch.float32
+    if x.dtype != want or w_packed.dtype != want:
+        raise _lib.BvgError(f"conv1d_nlc: operands must be {want} for this precision (x {x.dtype}, w {w_packed.dtype})")
+    y32 = torch.empty((B, T, Cout), dtype=torch.float32, device=x.device) if out_f32 else None
+    y16 = torch.empty((B, T, Cout), dtype=torch.bfloat16, device=x.device) if out_bf16 else None
+    with torch.cuda.device(x.device):
+        check(_lib.load().bvg_conv1d_nlc_fwd(x.data_ptr(), w_packed.data_ptr(), _ptr(bias), _ptr(residual), _ptr(accum),
+                                             _ptr(y32), _ptr(y16), B, T, Cin, Cout, k, dilation, float(out_scale),
+                                             precision, _stream()), "bvg_conv1d_nlc_fwd")
+    if out_f32 and out_bf16:
+        return y32, y16
+    return y32 if out_f32 else y16
+
+
+def convtranspose1d_nlc(x: torch.Tensor, w_packed: torch.Tensor, bias: Optional[torch.Tensor], K: int, stride: int,
+                        precision: int, out_f32: bool = True, out_bf16: bool = False):
+    _require_cuda(x, "convtranspose1d_nlc")
+    x = x.contiguous()
+    B, Tin, Cin = x.shape
+    taps, N, Cin2 = w_packed.shape
+    Cout = N // stride
+    if Cin2 != Cin or taps * stride != K:
+        raise _lib.BvgError("convtranspose1d_nlc: packed weight does not match x / K / stride")
+    y32 = torch.empty((B, Tin * stride, Cout), dtype=torch.float32, device=x.device) if out_f32 else None
+    y16 = torch.empty((B, Tin * stride, Cout), dtype=torch.bfloat16, device=x.device) if out_bf16 else None
+    with torch.cuda.device(x.device):
+        check(_lib.load().bvg_convtranspose1d_nlc_fwd(x.data_ptr(), w_packed.data_ptr(), _ptr(bias), _ptr(y32), _ptr(y16),
+                                                      B, Tin, Cin, Cout, K, stride, precision, _stream()),
+              "bvg_convtranspose1d_nlc_fwd")
+    if out_f32 and out_bf16:
+        return y32, y16
+    return y32 if out_f32 else y16
+
+
+def conv_post(x_nlc: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor], use_tanh: bool) -> torch.Tensor:
+    _require_cuda(x_nlc, "conv_post")
+    x_nlc = x_nlc.contiguous()
+    B, T, Cin = x_nlc.shape
+    w = w.detach().float().contiguous()
+    y = torch.empty((B, 1, T), dtype=torch.float32, device=x_nlc.device)
+    with torch.cuda.device(x_nlc.device):
+        check(_lib.load().bvg_conv_post_fwd(x_nlc.data_ptr(), w.data_ptr(), _ptr(bias), y.data_ptr(), B, T, Cin,
+                                            w.shape[-1], int(bool(use_tanh)), _stream()), "bvg_conv_post_fwd")
+    return y
+
+
+def launch_count() -> int:
+    return int(_lib.load().bvg_launch_count())
+
+
+def reset_launch_count():
+    _lib.load().bvg_reset_launch_count()

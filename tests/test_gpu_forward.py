@@ -1,0 +1,162 @@
+"""Whole-generator parity on a B200 through the reference-shaped module (BigVGAN.forward -> bvg_forward)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from helpers import MINI_H, O, build_model, snr_db
+
+pytestmark = pytest.mark.gpu
+
+
+def _check_fp32(ref, wav, what):
+    err = float(np.abs(wav - ref).max())
+    snr = snr_db(ref, wav)
+    print(f"{what}: fp32 max-abs {err:.3e}, SNR {snr:.1f} dB")
+    assert err <= 1e-4, what       # BASELINE.json: fp32 max-abs waveform error <= 1e-4
+    assert snr >= 80.0, what       # ... with SNR >= 80 dB
+
+
+def _check_bf16(ref, wav, what):
+    snr = snr_db(ref, wav)
+    print(f"{what}: bf16 SNR {snr:.1f} dB, max-abs {float(np.abs(wav - ref).max()):.3e}")
+    assert snr >= 40.0, what       # BASELINE.json: bf16 SNR >= 40 dB against the fp32 reference
+
+
+@pytest.mark.parametrize("form", ["wn", "plain"])
+def test_mini_generator_golden(golden_dir, form):
+    """Mini generator (initial channel 512), B = 2, ragged T = 23, reference outputs from tests/golden."""
+    g = np.load(os.path.join(golden_dir, f"mini_forward_{form}.npz"))
+    sd = O.make_state_dict(MINI_H, seed=int(g["seed"]), weight_norm=(form == "wn"))
+    m = build_model(MINI_H, sd, precision="fp32")
+    mel = torch.from_numpy(g["mel"]).cuda()
+    with torch.no_grad():
+        wav = m(mel).cpu().numpy()
+    assert wav.shape == g["wav"].shape
+    _check_fp32(g["wav64"], wav, f"mini/{form}")
+    m.set_precision("bf16")
+    with torch.no_grad():
+        wav = m(mel).cpu().numpy()
+    _check_bf16(g["wav64"], wav, f"mini/{form}")
+    if form == "wn":  # remove_weight_norm() afterwards must not change the result (re-pack path)
+        m.remove_weight_norm()
+        with torch.no_grad():
+            wav2 = m(mel).cpu().numpy()
+        assert snr_db(wav, wav2) > 60
+
+
+@pytest.fixture(scope="module")
+def full_models():
+    sd = O.make_state_dict(O.DEFAULT_HPARAMS, seed=11)
+    return sd, build_model(O.DEFAULT_HPARAMS, sd, precision="fp32")
+
+
+def test_full_generator_golden(golden_dir, full_models):
+    """bigvgan_v2_22khz_80band_256x (112 M parameters), reference outputs from tests/golden/full_forward.npz."""
+    g = np.load(os.path.join(golden_dir, "full_forward.npz"))
+    _, m = full_models
+    for tag in ("a", "b"):
+        mel = torch.from_numpy(g[f"mel_{tag}"]).cuda()
+        m.set_precision("fp32")
+        with torch.no_grad():
+            wav = m(mel).cpu().numpy()
+        _check_fp32(g[f"wav_{tag}"], wav, f"full/{tag}")
+        m.set_precision("bf16")
+        with torch.no_grad():
+            wav = m(mel).cpu().numpy()
+        _check_bf16(g[f"wav_{tag}"], wav, f"full/{tag}")
+
+
+def test_full_generator_clamp_path(golden_dir):
+    """1.3x weights + log-mel-like input: 16 % of the samples hit the final clamp(-1, 1)."""
+    g = np.load(os.path.join(golden_dir, "full_forward.npz"))
+    sd = O.make_state_dict(O.DEFAULT_HPARAMS, seed=int(g["seed_c"]), scale=float(g["scale_c"]))
+    m = build_model(O.DEFAULT_HPARAMS, sd, precision="fp32")
+    with torch.no_grad():
+        wav = m(torch.from_numpy(g["mel_c"]).cuda()).cpu().numpy()
+    assert np.abs(wav).max() <= 1.0 and (np.abs(wav) == 1.0).mean() > 0.05
+    # amplified weights amplify rounding too: the clamp path is checked at SNR >= 60 dB / max-abs 5e-3
+    assert snr_db(g["wav_c"], wav) >= 60.0 and np.abs(wav - g["wav_c"]).max() < 5e-3
+    m.set_precision("bf16")
+    with torch.no_grad():
+        wav = m(torch.from_numpy(g["mel_c"]).cuda()).cpu().numpy()
+    assert np.abs(wav).max() <= 1.0 and snr_db(g["wav_c"], wav) >= 25.0
+
+
+def test_cfg1_vs_oracle_and_module_contract(full_models):
+    """BASELINE.json configs[0]: one 5 s mel (80 x 431), batch 1, against the CPU oracle run here on the host cores.
+    Also: non-contiguous time-slice input, inference_mode input, output shape/dtype/range."""
+    sd, m = full_models
+    gen = torch.Generator().manual_seed(0)
+    mel_full = torch.randn(1, 80, 431 + 20, generator=gen)
+    mel = mel_full[:, :, 20:]                       # non-contiguous like infer_v2.py:856
+    ref = O.forward(sd, mel.numpy(), None, np.float32)
+    m.set_precision("fp32")
+    with torch.inference_mode():
+        wav = m(mel_full.cuda()[:, :, 20:])
+    assert tuple(wav.shape) == (1, 1, 431 * 256) and wav.dtype == torch.float32
+    assert float(wav.abs().max()) <= 1.0
+    _check_fp32(ref, wav.cpu().numpy(), "cfg1")
+    m.set_precision("bf16")
+    with torch.no_grad():
+        wav = m(mel.cuda()).cpu().numpy()
+    _check_bf16(ref, wav, "cfg1")
+
+
+def test_batch_items_are_independent_and_time_sharding(full_models):
+    """B > 1 with independent edges; time-sharding with the 38-frame halo equals the unsharded forward."""
+    _, m = full_models
+    m.set_precision("fp32")
+    gen = torch.Generator().manual_seed(5)
+    mel = torch.randn(3, 80, 100, generator=gen).cuda()
+    with torch.no_grad():
+        wav = m(mel)
+        one = m(mel[1:2])
+    assert torch.allclose(wav[1:2], one, atol=1e-6)
+    halo, hop = O.RECEPTIVE_HALO_FRAMES, 256
+    with torch.no_grad():
+        left = m(mel[:1, :, :50 + halo])[..., :50 * hop]
+        right = m(mel[:1, :, 50 - halo:])[..., halo * hop:]
+    stitched = torch.cat([left, right], dim=-1)
+    assert float((stitched - wav[:1]).abs().max()) <= 1e-6
+
+
+def test_empty_and_tiny_inputs(full_models):
+    _, m = full_models
+    m.set_precision("bf16")
+    with torch.no_grad():
+        assert tuple(m(torch.zeros(0, 80, 10, device="cuda")).shape) == (0, 1, 2560)
+        assert tuple(m(torch.zeros(2, 80, 0, device="cuda")).shape) == (2, 1, 0)
+        w = m(torch.randn(1, 80, 1, device="cuda"))
+    assert tuple(w.shape) == (1, 1, 256) and torch.isfinite(w).all()
+    with pytest.raises(ValueError):
+        m(torch.zeros(1, 81, 4, device="cuda"))
+
+
+def test_submodule_forwards_match_fused_plan(golden_dir):
+    """Calling the reference-shaped submodules one by one ([B,C,T] tensors, like the reference's own forward loop)
+    gives the same waveform as the fused bvg_forward plan."""
+    g = np.load(os.path.join(golden_dir, "mini_forward_plain.npz"))
+    sd = O.make_state_dict(MINI_H, seed=int(g["seed"]))
+    m = build_model(MINI_H, sd, precision="fp32")
+    mel = torch.from_numpy(g["mel"]).cuda()
+    with torch.no_grad():
+        x = m.conv_pre(mel)
+        np.testing.assert_allclose(x.cpu().numpy(), g["conv_pre"], atol=2e-5)
+        for i in range(m.num_upsamples):
+            x = m.ups[i][0](x)
+            if i == 0:
+                np.testing.assert_allclose(x.cpu().numpy(), g["ups0"], atol=2e-5)
+            xs = None
+            for j in range(m.num_kernels):
+                r = m.resblocks[i * m.num_kernels + j](x)
+                if i == 0 and j == 0:
+                    np.testing.assert_allclose(r.cpu().numpy(), g["rb0"], atol=5e-5)
+                xs = r if xs is None else xs + r
+            x = xs / m.num_kernels
+        x = m.activation_post(x)
+        full = m(mel)
+    from index_tts_b200 import ops
+    post = ops.conv_post(ops.ncl_to_nlc(x, torch.float32), m.conv_post.weight, None, False)
+    assert float((post - full).abs().max()) <= 2e-6

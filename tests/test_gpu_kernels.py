@@ -1,0 +1,240 @@
+"""Kernel-level parity on a B200: every libbvg kernel, called through the C ABI (via the ctypes wrappers in
+index_tts_b200.ops), against the CPU oracle on the same seeded inputs.  Tolerances are stated per test."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from helpers import O, rel_err, snr_db
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ops():
+    from index_tts_b200 import ops as _ops
+    return _ops
+
+
+def _t(a, dtype=torch.float32):
+    return torch.from_numpy(np.ascontiguousarray(a)).to("cuda", dtype)
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# Activation1d, public [B,C,T] layout
+# ---------------------------------------------------------------------------------------------------------------
+def test_activation1d_ncl_golden_fp32(ops, golden_dir):
+    """Reference's own Activation1d outputs (tests/golden/act1d.npz), fp32 precise mode: max-abs <= 2e-5
+    (inputs are ~N(0,2), outputs O(1..5); fp32 rounding of a 24-MAC pipeline + sin)."""
+    g = np.load(os.path.join(golden_dir, "act1d.npz"))
+    for i in range(int(g["n"])):
+        x, al, be = g[f"x{i}"], g[f"alpha{i}"], g[f"beta{i}"]
+        y = ops.activation1d(_t(x), _t(al), _t(be), True).cpu().numpy()
+        assert y.shape == x.shape
+        np.testing.assert_allclose(y, g[f"y64_{i}"], rtol=0, atol=2e-5, err_msg=f"case {i} shape {x.shape}")
+
+
+@pytest.mark.parametrize("T", [1, 7, 2047, 2048, 2049, 4096 + 37, 50000])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_activation1d_ncl_vs_oracle(ops, T, dtype):
+    """Tile edges (2048-sample tiles, 16 outputs per thread), odd T (unaligned rows -> scalar path), both IO dtypes.
+    fp32/precise: max-abs <= 2e-5.  bf16 IO / MUFU: output rounding dominates: <= 2^-7 relative to max |y|."""
+    rng = np.random.default_rng(T)
+    B, C = 2, 6
+    x = (rng.standard_normal((B, C, T)) * 1.5).astype(np.float32)
+    al = (0.5 * rng.standard_normal(C)).astype(np.float32)
+    be = (0.5 * rng.standard_normal(C)).astype(np.float32)
+    xt = _t(x, dtype)
+    ref = O.activation1d(xt.float().cpu().numpy().astype(np.float64), al, be)
+    y = ops.activation1d(xt, _t(al), _t(be), dtype == torch.float32)
+    assert y.dtype == dtype and tuple(y.shape) == (B, C, T)
+    y = y.float().cpu().numpy()
+    if dtype == torch.float32:
+        np.testing.assert_allclose(y, ref, rtol=0, atol=2e-5)
+    else:
+        assert rel_err(ref, y) < 2.0 ** -7
+        assert snr_db(ref, y) > 45
+
+
+def test_activation1d_ncl_fast_math_fp32(ops):
+    """MUFU path on fp32 IO: absolute error of cos.approx (~5e-7 * 1/b) -> max-abs <= 5e-5 for these inputs."""
+    rng = np.random.default_rng(3)
+    x = rng.standard_normal((1, 8, 5000)).astype(np.float32)
+    al = (0.5 * rng.standard_normal(8)).astype(np.float32)
+    be = (0.5 * rng.standard_normal(8)).astype(np.float32)
+    ref = O.activation1d(x.astype(np.float64), al, be)
+    y = ops.activation1d(_t(x), _t(al), _t(be), False).cpu().numpy()
+    np.testing.assert_allclose(y, ref, rtol=0, atol=5e-5)
+
+
+def test_activation1d_ncl_strided_input_and_empty(ops):
+    """Non-contiguous time slice (infer_v2.py:856 produces one) and empty input (reference: silent no-op)."""
+    rng = np.random.default_rng(4)
+    full = _t(rng.standard_normal((2, 8, 300)).astype(np.float32))
+    view = full[:, :, 37:]
+    assert not view.is_contiguous()
+    al = _t(np.zeros(8, np.float32))
+    y = ops.activation1d(view, al, al, True).cpu().numpy()
+    ref = O.activation1d(view.cpu().numpy().astype(np.float64), np.zeros(8, np.float32), np.zeros(8, np.float32))
+    np.testing.assert_allclose(y, ref, rtol=0, atol=2e-5)
+    e = ops.activation1d(torch.empty(2, 8, 0, device="cuda"), al, al, True)
+    assert tuple(e.shape) == (2, 8, 0)
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# Activation1d, channels-last
+# ---------------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("C", [8, 24, 48, 96, 192, 384, 768])
+@pytest.mark.parametrize("T", [1, 5, 64, 1000])
+def test_activation1d_nlc_vs_oracle_fp32(ops, C, T):
+    """All stage widths x segment-edge lengths; fp32 in/out precise: max-abs <= 2e-5."""
+    rng = np.random.default_rng(C * 1000 + T)
+    B = 2
+    x = (rng.standard_normal((B, C, T)) * 1.5).astype(np.float32)
+    al = (0.5 * rng.standard_normal(C)).astype(np.float32)
+    be = (0.5 * rng.standard_normal(C)).astype(np.float32)
+    ref = O.activation1d(x.astype(np.float64), al, be)
+    xn = _t(np.transpose(x, (0, 2, 1)))
+    y = ops.activation1d_nlc(xn, _t(al), _t(be), torch.float32, True).cpu().numpy()
+    np.testing.assert_allclose(np.transpose(y, (0, 2, 1)), ref, rtol=0, atol=2e-5)
+
+
+@pytest.mark.parametrize("in_dtype", [torch.float32, torch.bfloat16])
+def test_activation1d_nlc_bf16_out_long(ops, in_dtype):
+    """Long sequence (all segment lengths, interior + edge paths), MUFU path, bf16 output: error <= 2^-7 of max."""
+    rng = np.random.default_rng(11)
+    B, C, T = 3, 48, 40000
+    x = (rng.standard_normal((B, C, T)) * 1.5).astype(np.float32)
+    al = (0.5 * rng.standard_normal(C)).astype(np.float32)
+    be = (0.5 * rng.standard_normal(C)).astype(np.float32)
+    xn = _t(np.transpose(x, (0, 2, 1)), in_dtype)
+    ref = O.activation1d(np.transpose(xn.float().cpu().numpy(), (0, 2, 1)).astype(np.float64), al, be)
+    y = ops.activation1d_nlc(xn, _t(al), _t(be), torch.bfloat16, False).float().cpu().numpy()
+    y = np.transpose(y, (0, 2, 1))
+    assert rel_err(ref, y) < 2.0 ** -7 and snr_db(ref, y) > 45
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# layout + weight preparation
+# ---------------------------------------------------------------------------------------------------------------
+def test_transposes_and_weight_prep(ops):
+    rng = np.random.default_rng(5)
+    x = rng.standard_normal((2, 80, 77)).astype(np.float32)
+    y = ops.ncl_to_nlc(_t(x), torch.float32)
+    assert torch.equal(y.cpu(), torch.from_numpy(x).transpose(1, 2).contiguous())
+    z = ops.nlc_to_ncl(y, torch.float32)
+    assert torch.equal(z.cpu(), torch.from_numpy(x))
+    yb = ops.ncl_to_nlc(_t(x), torch.bfloat16)
+    assert torch.equal(yb.cpu(), torch.from_numpy(x).transpose(1, 2).contiguous().bfloat16())
+    # weight norm fold (dim 0), conv and transposed-conv packing
+    v = rng.standard_normal((16, 8, 7)).astype(np.float32)
+    g = rng.uniform(0.5, 2, (16, 1, 1)).astype(np.float32)
+    w = ops.fold_weight_norm(_t(v), _t(g)).cpu().numpy()
+    np.testing.assert_allclose(w, O.fold_weight_norm(v, g), rtol=2e-6, atol=0)
+    p = ops.pack_conv1d_weight(_t(v), 0).cpu().numpy()
+    np.testing.assert_array_equal(p, np.transpose(v, (2, 0, 1)))
+    wt = rng.standard_normal((8, 4, 8)).astype(np.float32)  # [Cin, Cout, K], u = 4
+    pt = ops.pack_convtranspose1d_weight(_t(wt), 4, 0).cpu().numpy()
+    assert pt.shape == (2, 16, 8)
+    for j in range(2):
+        for r in range(4):
+            kk = (r + 2) % 4 + 4 * (1 - j)
+            np.testing.assert_array_equal(pt[j, r * 4:(r + 1) * 4, :], wt[:, :, kk].T)
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# convolutions
+# ---------------------------------------------------------------------------------------------------------------
+CONV_CASES = [
+    # B, Cin, Cout, T, k, d
+    (2, 24, 24, 300, 3, 1), (1, 24, 24, 129, 11, 5), (1, 48, 48, 500, 7, 3), (2, 96, 96, 260, 11, 1),
+    (1, 192, 192, 140, 3, 5), (1, 384, 384, 200, 7, 1), (1, 768, 768, 150, 11, 3), (2, 80, 1536, 50, 7, 1),
+    (1, 16, 32, 5, 3, 1), (1, 8, 8, 1, 11, 5),
+]
+
+
+@pytest.mark.parametrize("case", CONV_CASES)
+def test_conv1d_exact_fp32(ops, case):
+    """BVG_EXACT_F32 conv vs fp64 oracle incl. bias + residual + scale + accum epilogue: <= 1e-5 of max |y|."""
+    B, Cin, Cout, T, k, d = case
+    rng = np.random.default_rng(hash(case) % 2 ** 31)
+    x = rng.standard_normal((B, Cin, T)).astype(np.float32)
+    w = (rng.standard_normal((Cout, Cin, k)) / np.sqrt(Cin * k)).astype(np.float32)
+    b = rng.standard_normal(Cout).astype(np.float32)
+    res = rng.standard_normal((B, Cout, T)).astype(np.float32)
+    acc = rng.standard_normal((B, Cout, T)).astype(np.float32)
+    ref = (O.conv1d(x.astype(np.float64), w.astype(np.float64), b, d) + res) / 3.0 + acc
+    wp = ops.pack_conv1d_weight(_t(w), 0)
+    y = ops.conv1d_nlc(_t(np.transpose(x, (0, 2, 1))), wp, _t(b), d, 0, residual=_t(np.transpose(res, (0, 2, 1))),
+                       accum=_t(np.transpose(acc, (0, 2, 1))), out_scale=1.0 / 3.0)
+    y = np.transpose(y.cpu().numpy(), (0, 2, 1))
+    assert rel_err(ref, y) < 1e-5
+
+
+@pytest.mark.parametrize("case", CONV_CASES)
+def test_conv1d_tcgen05_bf16(ops, case):
+    """BVG_BF16_TC conv (tcgen05, TMEM fp32 accumulation) on bf16-representable inputs vs fp64 oracle on the SAME
+    rounded operands: only accumulation order differs -> <= 2e-5 of max |y| (fp32 epilogue) and bf16 copy <= 2^-8."""
+    B, Cin, Cout, T, k, d = case
+    rng = np.random.default_rng(hash(case) % 2 ** 31 + 1)
+    x = torch.from_numpy(rng.standard_normal((B, Cin, T)).astype(np.float32)).bfloat16()
+    w = torch.from_numpy((rng.standard_normal((Cout, Cin, k)) / np.sqrt(Cin * k)).astype(np.float32)).bfloat16()
+    b = rng.standard_normal(Cout).astype(np.float32)
+    res = rng.standard_normal((B, Cout, T)).astype(np.float32)
+    ref = O.conv1d(x.float().numpy().astype(np.float64), w.float().numpy().astype(np.float64), b, d) + res
+    wp = ops.pack_conv1d_weight(w.float().cuda(), 1)
+    y32, y16 = ops.conv1d_nlc(x.cuda().transpose(1, 2).contiguous(), wp, _t(b), d, 1,
+                              residual=_t(np.transpose(res, (0, 2, 1))), out_f32=True, out_bf16=True)
+    y = np.transpose(y32.cpu().numpy(), (0, 2, 1))
+    assert rel_err(ref, y) < 2e-5
+    assert rel_err(ref, np.transpose(y16.float().cpu().numpy(), (0, 2, 1))) < 2.0 ** -8
+
+
+CONVT_CASES = [(2, 1536, 768, 20, 8, 4), (1, 768, 384, 70, 8, 4), (1, 384, 192, 130, 4, 2), (1, 192, 96, 129, 4, 2),
+               (2, 96, 48, 300, 4, 2), (1, 48, 24, 257, 4, 2), (1, 16, 8, 1, 8, 4)]
+
+
+@pytest.mark.parametrize("case", CONVT_CASES)
+@pytest.mark.parametrize("precision", [0, 1])
+def test_convtranspose1d_polyphase(ops, case, precision):
+    """Polyphase transposed conv (all six stage shapes) vs the oracle: exact mode <= 1e-5, tcgen05 mode <= 2e-5 of
+    max |y| on bf16-representable operands."""
+    B, Cin, Cout, T, K, u = case
+    rng = np.random.default_rng(hash(case) % 2 ** 31 + precision)
+    x = torch.from_numpy(rng.standard_normal((B, Cin, T)).astype(np.float32)).bfloat16().float()
+    w = torch.from_numpy((rng.standard_normal((Cin, Cout, K)) / np.sqrt(Cin * K / u)).astype(np.float32)).bfloat16().float()
+    b = rng.standard_normal(Cout).astype(np.float32)
+    ref = O.conv_transpose1d(x.numpy().astype(np.float64), w.numpy().astype(np.float64), b, u, (K - u) // 2)
+    wp = ops.pack_convtranspose1d_weight(w.cuda(), u, precision)
+    xin = x.cuda().transpose(1, 2).contiguous()
+    if precision == 1:
+        xin = xin.bfloat16()
+    y = ops.convtranspose1d_nlc(xin, wp, _t(b), K, u, precision)
+    assert tuple(y.shape) == (B, T * u, Cout)
+    y = np.transpose(y.cpu().numpy(), (0, 2, 1))
+    assert rel_err(ref, y) < (1e-5 if precision == 0 else 2e-5)
+
+
+def test_conv_post_clamp_and_tanh(ops):
+    rng = np.random.default_rng(9)
+    x = rng.standard_normal((2, 24, 999)).astype(np.float32)
+    w = rng.standard_normal((1, 24, 7)).astype(np.float32) * 0.2
+    ref = O.conv1d(x.astype(np.float64), w.astype(np.float64), None)
+    xn = _t(np.transpose(x, (0, 2, 1)))
+    y = ops.conv_post(xn, _t(w), None, False).cpu().numpy()
+    np.testing.assert_allclose(y, np.clip(ref, -1, 1), atol=2e-6)
+    assert (np.abs(y) == 1.0).mean() > 0.05
+    y = ops.conv_post(xn, _t(w), None, True).cpu().numpy()
+    np.testing.assert_allclose(y, np.tanh(ref), atol=2e-6)
+
+
+def test_errors_are_loud(ops):
+    from index_tts_b200 import _lib
+    with pytest.raises(_lib.BvgError):
+        ops.activation1d(torch.zeros(1, 8, 16), torch.zeros(8), torch.zeros(8), True)  # CPU tensor
+    with pytest.raises(_lib.BvgError):
+        ops.activation1d(torch.zeros(1, 8, 16, device="cuda", dtype=torch.float16), torch.zeros(8), torch.zeros(8), True)
+    with pytest.raises(_lib.BvgError):  # Cin not a multiple of 8
+        ops.conv1d_nlc(torch.zeros(1, 16, 12, device="cuda", dtype=torch.bfloat16),
+                       torch.zeros(3, 8, 12, device="cuda", dtype=torch.bfloat16), None, 1, 1)
