@@ -1,0 +1,304 @@
+#!/usr/bin/env python
+"""bench.py -- vocoder audio-seconds per wall-second (BASELINE.json metric) on N B200s of one node.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+A "step" is one BigVGAN forward over one batch of synthetic mels.  Workload at every N: BASELINE.json configs[1],
+batch 16 x 10 s mels (80 x 862 frames) per GPU, bf16 tensor-core mode, random-init weights of
+bigvgan_v2_22khz_80band_256x (weak scaling: utterances of a batch go to different GPUs, no data-path collective).
+
+Printed JSON line (rank 0):
+  value      audio-s/s with the mels already resident in HBM (CUDA events around each step, max over ranks)
+  e2e        same metric through the public module call with HOST mels: pinned H2D copy + forward + D2H of the wav
+  roofline   the dominant kernel (tcgen05 implicit-GEMM conv): algorithmic FLOPs of its launches / their CUDA-event
+             time, against the measured bf16 peak in MEASURED_PEAKS.json
+  cpu_baseline  the CPU oracle port (oracle/torch_port.py: the reference's op sequence on torch CPU kernels) timed on this box's host cores on a bounded sample
+--impl reference: the CPU arm only (the reference is Python/torch and cannot travel to the box; its restatement in
+oracle/ is timed with all host threads), same metric/config/unit.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+SR, HOP, NUM_MELS = 22050, 256, 80
+CFG2_B, CFG2_T = 16, 862
+WORKLOAD = "cfg2: bigvgan_v2_22khz_80band_256x random-init, batch 16 x 10 s synthetic mels (80x862) per GPU"
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return dict(hbm=float(d["hbm_gbs"]), tf=float(d["bf16_tflops"]), tf_sus=float(d.get("bf16_tflops_sustained", d["bf16_tflops"])),
+                    source="measured (MEASURED_PEAKS.json)")
+    return dict(hbm=6650.0, tf=1590.0, tf_sus=1400.0, source="fallback (B200_PROFILING.md)")
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled during the timed region."""
+
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], None, set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx = float(r[1])
+            except Exception:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        # samples under load = upper half of the distribution
+        sm.sort()
+        under = sm[len(sm) // 2:] if sm else []
+        return {"sm_mhz": statistics.median(under) if under else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def make_state_dict_torch(seed=1234):
+    """Random-init weights of the named architecture: the module's own seeded construction (identical to the
+    reference's, tests/test_abi.py), alpha/beta randomised N(0, 0.5) so per-channel indexing is exercised."""
+    import torch
+    from index_tts_b200 import bigvgan as B
+    h = B.load_hparams_from_json(os.path.join(ROOT, "index-tts_b200", "config.json"))
+    torch.manual_seed(seed)
+    m = B.BigVGAN(h, use_cuda_kernel=True)
+    g = torch.Generator().manual_seed(4321)
+    with torch.no_grad():
+        for n, p in m.named_parameters():
+            if n.endswith(".alpha") or n.endswith(".beta"):
+                p.copy_(0.5 * torch.randn(p.shape, generator=g))
+    m.remove_weight_norm()
+    return m.eval()
+
+
+def cpu_port_audio_s_per_s(steps=1, warmup=1, frames=None, threads=None):
+    """The reference's CPU path restated op for op on torch CPU kernels (oracle/torch_port.py), all host threads,
+    on a bounded sample of the workload: one utterance of `frames` mel frames per step."""
+    import numpy as np
+    import torch
+    from oracle import bigvgan_oracle as O, torch_port as TP
+    threads = threads or os.cpu_count()
+    torch.set_num_threads(threads)
+    frames = frames or 431  # 5 s (BASELINE.json configs[0]): 1/32 of the cfg2 batch
+    sd = TP.prepare(O.make_state_dict(O.DEFAULT_HPARAMS, seed=1))
+    mel = torch.from_numpy(np.random.default_rng(0).standard_normal((1, NUM_MELS, frames)).astype(np.float32))
+    for _ in range(warmup):
+        TP.forward(sd, mel)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        TP.forward(sd, mel)
+    dt = (time.perf_counter() - t0) / steps
+    audio_s = frames * HOP / SR
+    return audio_s / dt, dt, threads, (f"1 utterance x {frames} frames ({audio_s:.2f} s audio) per step, fp32, torch CPU "
+                                       f"kernels, {threads} threads")
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    v, dt, threads, sample = cpu_port_audio_s_per_s(steps=max(1, min(args.steps, 5)), warmup=min(args.warmup, 1))
+    line = {
+        "impl": "reference", "metric": "vocoder audio-sec/sec (RTF^-1)", "value": v, "unit": "audio-s/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": min(args.warmup, 1), "ms_per_step": dt * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "note": "CPU arm: bounded sample of the workload"},
+        "cpu_baseline": {"value": v, "unit": "audio-s/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": "audio-s/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line))
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=CFG2_B)
+    ap.add_argument("--frames", type=int, default=CFG2_T)
+    ap.add_argument("--precision", default="bf16")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--layer-table", default=None, help="write the per-launch table (JSON) to this path")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import torch
+    import torch.distributed as dist
+    from index_tts_b200 import bigvgan as B, ops
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a B200: libbvg has no CPU path (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    W = max(3, args.warmup)
+
+    model = make_state_dict_torch().to(dev)
+    model.set_precision(args.precision)
+    Bsz, T = args.batch, args.frames
+    gen = torch.Generator().manual_seed(1 + rank)
+    mel_host = torch.randn(Bsz, NUM_MELS, T, generator=gen).pin_memory()
+    mel_dev = mel_host.to(dev)
+    wav_host = torch.empty(Bsz, 1, T * HOP).pin_memory()
+    audio_s = Bsz * T * HOP / SR
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)  # > 126 MB L2
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+        barrier()
+        for e0, e1 in evs:
+            flush.fill_(1)            # L2 flush between timed iterations (untimed)
+            e0.record()
+            fn()
+            e1.record()
+        barrier()
+        ms = sum(e0.elapsed_time(e1) for e0, e1 in evs)
+        t = torch.tensor([ms], device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item()) / steps
+
+    def step_resident():
+        with torch.no_grad():
+            return model(mel_dev)
+
+    def step_e2e():
+        with torch.no_grad():
+            m = mel_host.to(dev, non_blocking=True)
+            w = model(m)
+            wav_host.copy_(w, non_blocking=True)
+
+    for _ in range(W):
+        step_resident()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    ops.reset_launch_count()
+    ms_step = timed(step_resident, args.steps)
+    launches = ops.launch_count()
+    clocks = sampler.stop() if rank == 0 else None
+    for _ in range(2):
+        step_e2e()
+    ms_e2e = timed(step_e2e, args.steps)
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+
+    peaks = load_peaks()
+    # per-launch table of the same plan, live, CUDA events on the launching stream
+    for _ in range(2):
+        B.profile_forward(model, mel_dev)
+    _, recs = B.profile_forward(model, mel_dev)
+    by = {}
+    roof_ms_total, meas_ms_total = 0.0, 0.0
+    for r in recs:
+        d = by.setdefault(r["kind"], {"ms": 0.0, "flops": 0.0, "bytes": 0.0, "n": 0, "roof_ms": 0.0})
+        roof = max(r["flops"] / (peaks["tf_sus"] * 1e12), r["bytes"] / (peaks["hbm"] * 1e9)) * 1e3
+        d["ms"] += r["ms"]; d["flops"] += r["flops"]; d["bytes"] += r["bytes"]; d["n"] += 1; d["roof_ms"] += roof
+        if r["kind"] != "layout":
+            roof_ms_total += roof
+            meas_ms_total += r["ms"]
+    conv = by.get("conv1d", {"ms": 1.0, "flops": 0.0, "n": 0})
+    convt = by.get("convtranspose1d", {"ms": 0.0, "flops": 0.0, "n": 0})
+    mma_ms = conv["ms"] + convt["ms"]
+    mma_flops = conv["flops"] + convt["flops"]
+    ach = mma_flops / (mma_ms * 1e-3) / 1e12 if mma_ms > 0 else 0.0
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    if os.path.exists(tpath):
+        try:
+            traffic = json.load(open(tpath)).get("conv_umma_kernel_bytes_per_launch")
+        except Exception:
+            traffic = None
+    roofline = {"bound": "tensor", "kernel": "conv_umma_kernel (tcgen05 implicit-GEMM conv + polyphase convT)",
+                "achieved": ach, "peak": peaks["tf_sus"], "unit": "TFLOP/s", "frac": ach / peaks["tf_sus"],
+                "traffic": traffic, "launches": conv["n"] + convt["n"], "share_of_step": mma_ms / max(sum(d["ms"] for d in by.values()), 1e-9),
+                "peak_source": peaks["source"] + ", sustained bf16 (kernel timed inside a long step)"}
+    act = by.get("activation1d")
+    kernels = {k: {"ms": round(d["ms"], 4), "launches": d["n"], "roofline_ms": round(d["roof_ms"], 4),
+                   "frac_of_per_layer_roofline": (d["roof_ms"] / d["ms"]) if d["ms"] > 0 else None} for k, d in by.items()}
+    if act:
+        kernels["activation1d"]["achieved_GBs_algorithmic"] = act["bytes"] / (act["ms"] * 1e-3) / 1e9
+        kernels["activation1d"]["hbm_peak_GBs"] = peaks["hbm"]
+    if args.layer_table:
+        os.makedirs(os.path.dirname(os.path.abspath(args.layer_table)), exist_ok=True)
+        json.dump({"workload": WORKLOAD, "batch": Bsz, "frames": T, "peaks": peaks, "records": recs}, open(args.layer_table, "w"), indent=1)
+
+    cpu = None
+    if not args.no_cpu_baseline:
+        v, dt, threads, sample = cpu_port_audio_s_per_s(steps=3, warmup=1)
+        cpu = {"value": v, "unit": "audio-s/s", "cores": threads, "kind": "port", "sample": sample}
+
+    line = {
+        "metric": "vocoder audio-sec/sec (RTF^-1)", "value": world * audio_s / (ms_step * 1e-3), "unit": "audio-s/s",
+        "n_gpus": world, "steps": args.steps, "warmup": W, "ms_per_step": ms_step, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "bf16" if args.precision == "bf16" else "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "batch_per_gpu": Bsz, "mel_frames": T, "audio_s_per_step_per_gpu": audio_s,
+                   "precision": args.precision, "l2": "256 MiB flush write between timed iterations (untimed)",
+                   "sharding": "batch items across GPUs, no collective"},
+        "e2e": {"value": world * audio_s / (ms_e2e * 1e-3), "unit": "audio-s/s", "ms_per_step": ms_e2e,
+                "h2d_bytes_per_step": mel_host.numel() * 4, "d2h_bytes_per_step": wav_host.numel() * 4},
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+        "roofline": roofline,
+        "per_layer_roofline": {"roofline_ms": roof_ms_total, "measured_ms": meas_ms_total,
+                               "frac": roof_ms_total / meas_ms_total if meas_ms_total > 0 else None,
+                               "definition": "sum over layers of max(FLOPs/bf16 sustained peak, algorithmic bytes/HBM peak) / sum of CUDA-event kernel times"},
+        "kernels": kernels,
+        "cpu_baseline": cpu,
+    }
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

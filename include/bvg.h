@@ -175,6 +175,26 @@ BVG_API size_t bvg_workspace_bytes(const bvg_model_desc* m_host, int64_t B, int6
 BVG_API int bvg_forward(const bvg_model_desc* m_host, const float* mel, int64_t mel_stride_b, int64_t mel_stride_c, float* wav,
                 int64_t B, int64_t T_mel, void* workspace, size_t workspace_bytes, void* stream);
 
+/* ---------------------------------------------------------------------------------------------------------- */
+/* measurement: the same launch plan as bvg_forward with a CUDA event pair around every kernel launch (recorded on
+ * `stream`).  Synchronises `stream` before returning -- a profiling entry point, not a product path.  Fills up to
+ * max_records host records in launch order; *n_records = number of launches.  flops / bytes are the ALGORITHMIC
+ * work of the reference layer the launch implements (bf16 IO element size in BVG_BF16_TC mode,
+ * fp32 in BVG_EXACT_F32 mode; intermediates at the 2x rate and padding are not counted).                        */
+typedef enum { BVG_K_LAYOUT = 0, BVG_K_CONV1D = 1, BVG_K_CONVT = 2, BVG_K_ACT = 3, BVG_K_POST = 4 } bvg_launch_kind;
+typedef struct {
+    int32_t kind;          /* bvg_launch_kind */
+    int32_t stage;         /* -1 = pre / post, else upsample stage */
+    int32_t cin, cout, k, dilation;
+    int64_t rows;          /* B * T of the layer's output */
+    double flops, bytes;   /* algorithmic */
+    float ms;              /* measured with CUDA events on `stream` */
+} bvg_launch_record;
+
+BVG_API int bvg_forward_profile(const bvg_model_desc* m_host, const float* mel, int64_t mel_stride_b, int64_t mel_stride_c,
+                        float* wav, int64_t B, int64_t T_mel, void* workspace, size_t workspace_bytes, void* stream,
+                        bvg_launch_record* records_host, int max_records, int* n_records);
+
 #ifdef __cplusplus
 }
 #endif

@@ -48,6 +48,14 @@ class ModelDesc(C.Structure):
     ]
 
 
+class LaunchRecord(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("stage", C.c_int32), ("cin", C.c_int32), ("cout", C.c_int32), ("k", C.c_int32),
+                ("dilation", C.c_int32), ("rows", C.c_int64), ("flops", C.c_double), ("bytes", C.c_double),
+                ("ms", C.c_float)]
+
+
+KIND_NAMES = {0: "layout", 1: "conv1d", 2: "convtranspose1d", 3: "activation1d", 4: "conv_post"}
+
 # name -> (restype, argtypes); must list every symbol include/bvg.h declares (tests/test_abi.py checks that)
 SIGNATURES = {
     "bvg_last_error": (C.c_char_p, []),
@@ -69,6 +77,8 @@ SIGNATURES = {
     "bvg_conv_post_fwd": (c_int, [c_vp, c_vp, c_vp, c_vp, c_i64, c_i64, c_i64, c_int, c_int, c_vp]),
     "bvg_workspace_bytes": (c_sz, [C.POINTER(ModelDesc), c_i64, c_i64]),
     "bvg_forward": (c_int, [C.POINTER(ModelDesc), c_vp, c_i64, c_i64, c_vp, c_i64, c_i64, c_vp, c_sz, c_vp]),
+    "bvg_forward_profile": (c_int, [C.POINTER(ModelDesc), c_vp, c_i64, c_i64, c_vp, c_i64, c_i64, c_vp, c_sz, c_vp,
+                                    C.POINTER(LaunchRecord), c_int, C.POINTER(c_int)]),
 }
 
 _lock = threading.Lock()

@@ -327,6 +327,31 @@ class _PackedGenerator:
         return wav
 
 
+def profile_forward(model: "BigVGAN", mel: torch.Tensor):
+    """Measurement helper (bench.py): one forward with a CUDA event pair around every kernel launch
+    (``bvg_forward_profile``).  Returns ``(wav, records)``; each record is a dict with the launch kind, layer shape,
+    algorithmic flops/bytes and measured milliseconds."""
+    lib = _lib.load()
+    plan = model._plan(mel.device)
+    B, _, T = mel.shape
+    wav = torch.empty((B, 1, T * plan.hop), dtype=torch.float32, device=mel.device)
+    ws_bytes = lib.bvg_workspace_bytes(ctypes.byref(plan.desc), B, T)
+    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=mel.device)
+    recs = (_lib.LaunchRecord * 1024)()
+    n = ctypes.c_int(0)
+    mel = mel.float().contiguous()
+    with torch.cuda.device(mel.device):
+        _lib.check(lib.bvg_forward_profile(ctypes.byref(plan.desc), mel.data_ptr(), mel.stride(0), mel.stride(1),
+                                           wav.data_ptr(), B, T, ws.data_ptr(), ws_bytes,
+                                           torch.cuda.current_stream().cuda_stream, recs, 1024, ctypes.byref(n)),
+                   "bvg_forward_profile")
+    out = []
+    for r in recs[:min(n.value, 1024)]:
+        out.append(dict(kind=_lib.KIND_NAMES.get(r.kind, str(r.kind)), stage=r.stage, cin=r.cin, cout=r.cout, k=r.k,
+                        dilation=r.dilation, rows=r.rows, flops=r.flops, bytes=r.bytes, ms=r.ms))
+    return wav, out
+
+
 @torch.library.custom_op("bvg::vocoder_forward", mutates_args=())
 def _vocoder_forward(mel: torch.Tensor, plan_id: int, hop: int) -> torch.Tensor:
     plan = _PLANS.get(plan_id)

@@ -1,6 +1,8 @@
 // C-ABI entry points for the convolutions and the whole-generator launch plan (reference bigvgan.py:360-386).
 #include "bvg_common.cuh"
 
+#include <vector>
+
 namespace bvg {
 int conv_umma_launch(const void* x, const void* w_packed, const float* bias, const float* residual, const float* accum,
                      float* y_f32, void* y_bf16, int64_t B, int64_t T, int64_t Cin, int64_t N, int64_t cout_phase,
@@ -56,6 +58,33 @@ struct Plan {
 };
 
 static size_t align256(size_t v) { return (v + 255) & ~size_t(255); }
+
+// ---- optional per-launch timing (bvg_forward_profile) -------------------------------------------------------
+struct ProfEntry {
+    bvg_launch_record rec;
+    cudaEvent_t e0, e1;
+};
+static thread_local std::vector<ProfEntry>* g_prof = nullptr;
+
+struct ProfScope {
+    cudaStream_t st;
+    bool on;
+    ProfScope(int kind, int stage, int cin, int cout, int k, int dil, int64_t rows, double flops, double bytes,
+              cudaStream_t s)
+        : st(s), on(g_prof != nullptr) {
+        if (!on) return;
+        ProfEntry e{};
+        e.rec.kind = kind; e.rec.stage = stage; e.rec.cin = cin; e.rec.cout = cout; e.rec.k = k; e.rec.dilation = dil;
+        e.rec.rows = rows; e.rec.flops = flops; e.rec.bytes = bytes; e.rec.ms = 0.f;
+        cudaEventCreate(&e.e0);
+        cudaEventCreate(&e.e1);
+        cudaEventRecord(e.e0, st);
+        g_prof->push_back(e);
+    }
+    ~ProfScope() {
+        if (on) cudaEventRecord(g_prof->back().e1, st);
+    }
+};
 
 static int make_plan(const bvg_model_desc* m, int64_t B, int64_t T_mel, Plan* pl) {
     BVG_REQUIRE(m != nullptr, BVG_ERR_INVALID, "null model descriptor");
@@ -141,12 +170,22 @@ extern "C" int bvg_forward(const bvg_model_desc* m, const float* mel, int64_t me
     float* SUM = reinterpret_cast<float*>(ws + pl.off_sum);
     void* SUMOP = ws + pl.off_sumop;
 
+    const double es = tc ? 2.0 : 4.0;  // SURVEY.md 8(d) element size of the mode
+    auto conv_flops = [](double cin, double cout, double k, double rows) { return 2.0 * cin * cout * k * rows; };
+    auto conv_bytes = [&](double cin, double cout, double k, double rows, bool res) {
+        return es * rows * (cin + cout) + es * cin * cout * k + 4.0 * cout + (res ? es * rows * cout : 0.0);
+    };
     // mel [B, num_mels, T] -> [B, T, num_mels] in the operand dtype
+    {
+    ProfScope ps(BVG_K_LAYOUT, -1, m->num_mels, m->num_mels, 0, 0, B * T_mel, 0.0, 0.0, st);
     rc = transpose_any(mel, BVG_F32, mel_nlc, op_dt, B, m->num_mels, T_mel, mel_stride_b, mel_stride_c, st);
+    }
     if (rc != BVG_OK) return rc;
     // conv_pre (bigvgan.py:362): output feeds the first transposed conv directly -> operand dtype
     {
         const bvg_conv_desc& c = m->conv_pre;
+        ProfScope ps(BVG_K_CONV1D, -1, c.cin, c.cout, c.k, 1, B * T_mel, conv_flops(c.cin, c.cout, c.k, (double)B * T_mel),
+                     conv_bytes(c.cin, c.cout, c.k, (double)B * T_mel, false), st);
         rc = conv1d(prec, mel_nlc, c.w, c.bias, nullptr, nullptr, tc ? nullptr : reinterpret_cast<float*>(pre),
                     tc ? pre : nullptr, B, T_mel, c.cin, c.cout, c.k, 1, 1.0f, st);
         if (rc != BVG_OK) return rc;
@@ -160,7 +199,12 @@ extern "C" int bvg_forward(const bvg_model_desc* m, const float* mel, int64_t me
         const int u = m->upsample_rates[i];
         BVG_REQUIRE(up.cin == C && up.cout == C / 2, BVG_ERR_INVALID, "ups[%d]: channel mismatch", i);
         // upsample (bigvgan.py:366-367): fp32 residual stream X
-        rc = convtranspose1d(prec, stage_in, up.w, up.bias, X, nullptr, B, T, C, C / 2, up.k, u, st);
+        {
+            const double rin = (double)B * T;
+            ProfScope ps(BVG_K_CONVT, i, C, C / 2, up.k, 1, B * T * u, 2.0 * C * (C / 2) * up.k * rin,
+                         es * rin * (C + (C / 2) * (double)u) + es * (double)C * (C / 2) * up.k, st);
+            rc = convtranspose1d(prec, stage_in, up.w, up.bias, X, nullptr, B, T, C, C / 2, up.k, u, st);
+        }
         if (rc != BVG_OK) return rc;
         T *= u;
         C /= 2;
@@ -172,15 +216,29 @@ extern "C" int bvg_forward(const bvg_model_desc* m, const float* mel, int64_t me
                 const bvg_conv_desc& c2 = m->convs2[i][j][l];
                 const bvg_act_desc& a1 = m->acts[i][j][2 * l];
                 const bvg_act_desc& a2 = m->acts[i][j][2 * l + 1];
-                rc = activation1d_nlc(xr, BVG_F32, A, op_dt, a1.alpha_log, a1.beta_log, B, T, C, precise, st);
+                const double rows = (double)B * T;
+                const double act_flops = 62.0 * rows * C, act_bytes = 2.0 * es * rows * C + 8.0 * C;
+                {
+                    ProfScope ps(BVG_K_ACT, i, C, C, 0, 0, B * T, act_flops, act_bytes, st);
+                    rc = activation1d_nlc(xr, BVG_F32, A, op_dt, a1.alpha_log, a1.beta_log, B, T, C, precise, st);
+                }
                 if (rc != BVG_OK) return rc;
                 // xt between c1 and a2 is an intermediate (not the residual stream): operand dtype (bf16 in TC mode;
                 // costs ~1.2 dB of the 43.8 dB budget, tools/emulate_bf16_plan.py)
-                rc = conv1d(prec, A, c1.w, c1.bias, nullptr, nullptr, tc ? nullptr : reinterpret_cast<float*>(Y1),
-                            tc ? Y1 : nullptr, B, T, C, C, c1.k, c1.dilation, 1.0f, st);
+                {
+                    ProfScope ps(BVG_K_CONV1D, i, C, C, c1.k, c1.dilation, B * T, conv_flops(C, C, c1.k, rows),
+                                 conv_bytes(C, C, c1.k, rows, false), st);
+                    rc = conv1d(prec, A, c1.w, c1.bias, nullptr, nullptr, tc ? nullptr : reinterpret_cast<float*>(Y1),
+                                tc ? Y1 : nullptr, B, T, C, C, c1.k, c1.dilation, 1.0f, st);
+                }
                 if (rc != BVG_OK) return rc;
-                rc = activation1d_nlc(Y1, op_dt, A, op_dt, a2.alpha_log, a2.beta_log, B, T, C, precise, st);
+                {
+                    ProfScope ps(BVG_K_ACT, i, C, C, 0, 0, B * T, act_flops, act_bytes, st);
+                    rc = activation1d_nlc(Y1, op_dt, A, op_dt, a2.alpha_log, a2.beta_log, B, T, C, precise, st);
+                }
                 if (rc != BVG_OK) return rc;
+                ProfScope ps(BVG_K_CONV1D, i, C, C, c2.k, 1, B * T, conv_flops(C, C, c2.k, rows),
+                             conv_bytes(C, C, c2.k, rows, true), st);
                 const bool last = (l + 1 == m->num_dilations);
                 if (!last) {
                     // x = xt + x
@@ -199,9 +257,40 @@ extern "C" int bvg_forward(const bvg_model_desc* m, const float* mel, int64_t me
         stage_in = tc ? SUMOP : static_cast<const void*>(SUM);
     }
     // activation_post -> conv_post -> clamp / tanh (bigvgan.py:378-384), fp32 in both modes
-    rc = activation1d_nlc(SUM, BVG_F32, R, BVG_F32, m->act_post.alpha_log, m->act_post.beta_log, B, T, C, precise, st);
+    {
+        const double rows = (double)B * T;
+        ProfScope ps(BVG_K_ACT, -1, C, C, 0, 0, B * T, 62.0 * rows * C, 2.0 * es * rows * C + 8.0 * C, st);
+        rc = activation1d_nlc(SUM, BVG_F32, R, BVG_F32, m->act_post.alpha_log, m->act_post.beta_log, B, T, C, precise, st);
+    }
     if (rc != BVG_OK) return rc;
     const bvg_conv_desc& cp = m->conv_post;
     BVG_REQUIRE(cp.cout == 1 && cp.cin == C, BVG_ERR_UNSUPPORTED, "conv_post must map %d channels to 1", C);
+    ProfScope ps(BVG_K_POST, -1, C, 1, cp.k, 1, B * T, 2.0 * C * cp.k * (double)B * T, es * (double)B * T * (C + 1.0), st);
     return bvg_conv_post_fwd(R, static_cast<const float*>(cp.w), cp.bias, wav, B, T, C, cp.k, m->use_tanh_at_final, stream);
+}
+
+extern "C" int bvg_forward_profile(const bvg_model_desc* m, const float* mel, int64_t mel_stride_b, int64_t mel_stride_c,
+                                   float* wav, int64_t B, int64_t T_mel, void* workspace, size_t workspace_bytes,
+                                   void* stream, bvg_launch_record* records_host, int max_records, int* n_records) {
+    BVG_REQUIRE(records_host && n_records && max_records >= 0, BVG_ERR_INVALID, "bvg_forward_profile: null record buffer");
+    std::vector<ProfEntry> entries;
+    entries.reserve(512);
+    g_prof = &entries;
+    const int rc = bvg_forward(m, mel, mel_stride_b, mel_stride_c, wav, B, T_mel, workspace, workspace_bytes, stream);
+    g_prof = nullptr;
+    cudaError_t e = cudaStreamSynchronize(static_cast<cudaStream_t>(stream));
+    int n = 0;
+    for (auto& en : entries) {
+        float ms = 0.f;
+        if (e == cudaSuccess) cudaEventElapsedTime(&ms, en.e0, en.e1);
+        en.rec.ms = ms;
+        if (n < max_records) records_host[n] = en.rec;
+        ++n;
+        cudaEventDestroy(en.e0);
+        cudaEventDestroy(en.e1);
+    }
+    *n_records = n;
+    if (rc != BVG_OK) return rc;
+    if (e != cudaSuccess) return set_error(BVG_ERR_CUDA, "bvg_forward_profile: %s", cudaGetErrorString(e));
+    return BVG_OK;
 }
