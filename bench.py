@@ -172,7 +172,9 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
     W = max(3, args.warmup)
 
-    model = make_state_dict_torch().to(dev)
+    import contextlib
+    with contextlib.redirect_stdout(sys.stderr):  # the reference's remove_weight_norm() prints; stdout carries ONE JSON line
+        model = make_state_dict_torch().to(dev)
     model.set_precision(args.precision)
     Bsz, T = args.batch, args.frames
     gen = torch.Generator().manual_seed(1 + rank)

@@ -18,7 +18,8 @@
 // tensor and no wasted MACs.
 //
 // Warp-specialised persistent CTAs (1 per SM):  warp 0 = TMA producer, warp 1 = UMMA issuer (+ TMEM allocator),
-// warps 2..5 = epilogue (tcgen05.ld -> +bias +residual, *scale, +accum -> fp32 and/or bf16 global stores).
+// warps 2..5 = epilogue (tcgen05.ld -> +bias +residual, *scale, +accum -> swizzled smem -> TMA tensor stores),
+// warp 6 = TMA loader of the fp32 residual / accum chunks the epilogue consumes.
 // Pipelines: A ring (one halo tile per K-block), B ring (one weight tile per K-block x tap), two TMEM accumulators
 // so the epilogue of tile i overlaps the MMAs of tile i+1.
 #include "bvg_common.cuh"
@@ -28,8 +29,12 @@ namespace bvg {
 
 constexpr int UMMA_BLOCK_M = 128;
 constexpr int UMMA_BLOCK_K = 64;  // bf16 elements per 128-byte swizzled row
-constexpr int UMMA_THREADS = 192;
+constexpr int UMMA_THREADS = 224;  // 7 warps: TMA producer, UMMA issuer, 4 epilogue, residual loader
 constexpr int UMMA_MAX_STAGES = 8;
+constexpr int EPI_CHUNK = 32;                  // accumulator columns per epilogue step (= one 128-byte fp32 row segment)
+constexpr int EPI_LD_TILE_BYTES = 128 * 128;   // one residual / accum chunk: 128 rows x 32 fp32, 128B-swizzled
+constexpr int EPI_ST32_TILE_BYTES = 32 * 128;  // per-warp fp32 output chunk: 32 rows x 32 fp32, 128B-swizzled
+constexpr int EPI_ST16_TILE_BYTES = 32 * 64;   // per-warp bf16 output chunk: 32 rows x 32 bf16, 64B-swizzled
 
 struct ConvUmmaParams {
     const float* bias;      // [cout_phase] or null
@@ -50,41 +55,46 @@ struct ConvUmmaParams {
     int num_phases;
     int64_t m_tiles;  // ceil(T / 128)
     int64_t total_tiles;
-    int a_rows;      // rows of the A halo tile = 128 + (taps-1)*dil rounded up to 8
     int a_stages, b_stages;
     uint32_t a_stage_bytes, b_stage_bytes;
     uint32_t tmem_cols;
+    // weight-stationary mode: every (n tile, K block, tap) weight tile is loaded into shared memory ONCE per CTA and
+    // only the activation halo tiles stream (small-channel layers, where re-streaming weights per 128-row tile made
+    // the kernel TMA-latency bound)
+    int stationary;
+    uint32_t w_bytes;  // bytes of the stationary weight region
+    // epilogue I/O is all TMA: residual / accum chunks are prefetched by a loader warp, outputs leave through
+    // per-warp swizzled smem tiles and bulk tensor stores
+    int has_res, has_acc, has_y32, has_y16;
+    int ld_stages;     // residual/accum chunk ring depth (1 or 2)
     float out_scale;
 };
 
-// smem carve-up: [A ring][B ring][barriers][tmem ptr]
-struct SmemLayout {
-    uint32_t a_off, b_off, bar_off, total;
-};
-static inline SmemLayout smem_layout(const ConvUmmaParams& p) {
-    SmemLayout l;
-    l.a_off = 0;
-    l.b_off = p.a_stages * p.a_stage_bytes;
-    l.bar_off = l.b_off + p.b_stages * p.b_stage_bytes;
-    l.total = l.bar_off + (2 * UMMA_MAX_STAGES * 2 + 4) * 8 + 16;
-    return l;
-}
-
 __global__ void __launch_bounds__(UMMA_THREADS, 1)
 conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_w,
+                 const __grid_constant__ CUtensorMap map_res, const __grid_constant__ CUtensorMap map_acc,
+                 const __grid_constant__ CUtensorMap map_y32, const __grid_constant__ CUtensorMap map_y16,
                  const __grid_constant__ ConvUmmaParams p) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    // carve-up: [A ring][B ring | stationary weights][residual/accum chunk ring][fp32 out tiles][bf16 out tiles]
+    //           [barriers][tmem ptr]
     uint8_t* sA = smem;
-    uint8_t* sB = smem + p.a_stages * p.a_stage_bytes;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(sB + p.b_stages * p.b_stage_bytes);
+    uint8_t* sB = sA + p.a_stages * p.a_stage_bytes;
+    uint8_t* sLd = sB + (p.stationary ? p.w_bytes : p.b_stages * p.b_stage_bytes);
+    const int n_ld = p.has_res + p.has_acc;
+    uint8_t* sSt32 = sLd + p.ld_stages * n_ld * EPI_LD_TILE_BYTES;
+    uint8_t* sSt16 = sSt32 + (p.has_y32 ? 4 * 2 * EPI_ST32_TILE_BYTES : 0);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sSt16 + (p.has_y16 ? 4 * 2 * EPI_ST16_TILE_BYTES : 0));
     uint64_t* a_full = bars;
     uint64_t* a_empty = bars + UMMA_MAX_STAGES;
-    uint64_t* b_full = bars + 2 * UMMA_MAX_STAGES;
+    uint64_t* b_full = bars + 2 * UMMA_MAX_STAGES;   // [0] doubles as "weights resident" in stationary mode
     uint64_t* b_empty = bars + 3 * UMMA_MAX_STAGES;
-    uint64_t* acc_full = bars + 4 * UMMA_MAX_STAGES;   // [2]
-    uint64_t* acc_empty = acc_full + 2;                // [2]
-    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(acc_empty + 2);
+    uint64_t* acc_full = bars + 4 * UMMA_MAX_STAGES;  // [2]
+    uint64_t* acc_empty = acc_full + 2;               // [2]
+    uint64_t* ld_full = acc_empty + 2;                // [2]
+    uint64_t* ld_empty = ld_full + 2;                 // [2]
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(ld_empty + 2);
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -92,9 +102,14 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
     if (threadIdx.x == 0) {
         tma_prefetch_desc(&map_x);
         tma_prefetch_desc(&map_w);
-        for (int i = 0; i < p.a_stages; ++i) { mbar_init(&a_full[i], 1); mbar_init(&a_empty[i], 1); }
-        for (int i = 0; i < p.b_stages; ++i) { mbar_init(&b_full[i], 1); mbar_init(&b_empty[i], 1); }
-        for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 4); }
+        for (int i = 0; i < UMMA_MAX_STAGES; ++i) {
+            mbar_init(&a_full[i], 1); mbar_init(&a_empty[i], 1);
+            mbar_init(&b_full[i], 1); mbar_init(&b_empty[i], 1);
+        }
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 4);
+            mbar_init(&ld_full[i], 1); mbar_init(&ld_empty[i], 4);
+        }
         fence_barrier_init();
     }
     if (warp == 1) tmem_alloc(tmem_ptr, p.tmem_cols);
@@ -109,6 +124,16 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
     if (warp == 0) {
         // ------------------------------ TMA producer ------------------------------
         if (lane == 0) {
+            if (p.stationary) {
+                mbar_arrive_expect_tx(&b_full[0], p.w_bytes);
+                for (int nt = 0; nt < n_tiles; ++nt) {
+                    const int n0 = (nt / p.tiles_per_phase) * p.cout_phase + (nt % p.tiles_per_phase) * p.n_tile;
+                    for (int kb = 0; kb < k_blocks; ++kb)
+                        for (int j = 0; j < p.taps; ++j)
+                            tma_load_3d_hint(sB + ((nt * k_blocks + kb) * p.taps + j) * p.b_stage_bytes, &map_w, &b_full[0],
+                                             kb * UMMA_BLOCK_K, n0, j, kPolicyEvictLast);
+                }
+            }
             int sa = 0, sb = 0;
             uint32_t pa = 0, pb = 0;
             for (int64_t tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
@@ -124,12 +149,14 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                     mbar_arrive_expect_tx(&a_full[sa], p.a_stage_bytes);
                     tma_load_3d(sA + sa * p.a_stage_bytes, &map_x, &a_full[sa], kb * UMMA_BLOCK_K, row0, b);
                     if (++sa == p.a_stages) { sa = 0; pa ^= 1; }
-                    for (int j = 0; j < p.taps; ++j) {
-                        mbar_wait(&b_empty[sb], pb ^ 1);
-                        mbar_arrive_expect_tx(&b_full[sb], p.b_stage_bytes);
-                        tma_load_3d_hint(sB + sb * p.b_stage_bytes, &map_w, &b_full[sb], kb * UMMA_BLOCK_K, n0, j,
-                                         kPolicyEvictLast);
-                        if (++sb == p.b_stages) { sb = 0; pb ^= 1; }
+                    if (!p.stationary) {
+                        for (int j = 0; j < p.taps; ++j) {
+                            mbar_wait(&b_empty[sb], pb ^ 1);
+                            mbar_arrive_expect_tx(&b_full[sb], p.b_stage_bytes);
+                            tma_load_3d_hint(sB + sb * p.b_stage_bytes, &map_w, &b_full[sb], kb * UMMA_BLOCK_K, n0, j,
+                                             kPolicyEvictLast);
+                            if (++sb == p.b_stages) { sb = 0; pb ^= 1; }
+                        }
                     }
                 }
             }
@@ -140,7 +167,9 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
             const uint32_t idesc = umma_idesc_bf16_f32(UMMA_BLOCK_M, p.n_tile);
             int sa = 0, sb = 0, acc = 0;
             uint32_t pa = 0, pb = 0, pacc = 0;
+            if (p.stationary) mbar_wait(&b_full[0], 0);
             for (int64_t tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+                const int nt = static_cast<int>(tile % n_tiles);
                 mbar_wait(&acc_empty[acc], pacc ^ 1);
                 tc_fence_after_sync();
                 const uint32_t d_tmem = tmem_base + acc * p.n_tile;
@@ -149,19 +178,27 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                     const int k_rem = p.Cin - kb * UMMA_BLOCK_K;
                     const int k_steps = (min(k_rem, UMMA_BLOCK_K) + 15) / 16;
                     mbar_wait(&a_full[sa], pa);
+                    tc_fence_after_sync();
                     const uint32_t a_addr = smem_u32(sA + sa * p.a_stage_bytes);
                     for (int j = 0; j < p.taps; ++j) {
-                        mbar_wait(&b_full[sb], pb);
-                        tc_fence_after_sync();
-                        const uint32_t b_addr = smem_u32(sB + sb * p.b_stage_bytes);
+                        uint32_t b_addr;
+                        if (p.stationary) {
+                            b_addr = smem_u32(sB + ((nt * k_blocks + kb) * p.taps + j) * p.b_stage_bytes);
+                        } else {
+                            mbar_wait(&b_full[sb], pb);
+                            tc_fence_after_sync();
+                            b_addr = smem_u32(sB + sb * p.b_stage_bytes);
+                        }
                         const uint32_t a_tap = a_addr + static_cast<uint32_t>(j * p.dil) * 128u;
                         for (int ks = 0; ks < k_steps; ++ks) {
                             umma_f16(d_tmem, umma_desc_sw128_kmajor(a_tap + ks * 32), umma_desc_sw128_kmajor(b_addr + ks * 32),
                                      idesc, accumulate);
                             accumulate = 1;
                         }
-                        umma_commit(&b_empty[sb]);
-                        if (++sb == p.b_stages) { sb = 0; pb ^= 1; }
+                        if (!p.stationary) {
+                            umma_commit(&b_empty[sb]);
+                            if (++sb == p.b_stages) { sb = 0; pb ^= 1; }
+                        }
                     }
                     umma_commit(&a_empty[sa]);
                     if (++sa == p.a_stages) { sa = 0; pa ^= 1; }
@@ -170,80 +207,145 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                 if (++acc == 2) { acc = 0; pacc ^= 1; }
             }
         }
+    } else if (warp == 6) {
+        // ------------------------------ residual / accum chunk loader ------------------------------
+        if (lane == 0 && n_ld > 0) {
+            int s = 0;
+            uint32_t ps = 0;
+            for (int64_t tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+                const int nt = static_cast<int>(tile % n_tiles);
+                const int64_t rest = tile / n_tiles;
+                const int t0 = static_cast<int>((rest % p.m_tiles) * UMMA_BLOCK_M);
+                const int b = static_cast<int>(rest / p.m_tiles);
+                const int phase = nt / p.tiles_per_phase;
+                const int c0 = (nt % p.tiles_per_phase) * p.n_tile;
+                for (int c = 0; c < p.n_tile; c += EPI_CHUNK) {
+                    mbar_wait(&ld_empty[s], ps ^ 1);
+                    mbar_arrive_expect_tx(&ld_full[s], n_ld * EPI_LD_TILE_BYTES);
+                    uint8_t* dst = sLd + s * n_ld * EPI_LD_TILE_BYTES;
+                    if (p.has_res) tma_load_4d(dst, &map_res, &ld_full[s], c0 + c, phase, t0, b);
+                    if (p.has_acc) tma_load_4d(dst + p.has_res * EPI_LD_TILE_BYTES, &map_acc, &ld_full[s], c0 + c, phase, t0, b);
+                    if (++s == p.ld_stages) { s = 0; ps ^= 1; }
+                }
+            }
+        }
     } else {
         // ------------------------------ epilogue (warps 2..5) ------------------------------
-        const int q = warp & 3;  // TMEM lane quarter this warp may access
-        int acc = 0;
-        uint32_t pacc = 0;
+        // thread = accumulator row.  tcgen05.ld -> +bias (+residual chunk from smem) * scale (+accum chunk) -> swizzled
+        // per-warp smem tiles -> TMA bulk tensor stores.  No direct global loads/stores except the bias broadcast.
+        const int q = warp & 3;                 // TMEM lane quarter this warp may access
+        const int row = q * 32 + lane;          // row inside the 128-row tile
+        const uint32_t sw128 = static_cast<uint32_t>(row & 7);
+        const uint32_t sw64 = static_cast<uint32_t>((lane >> 1) & 3);
+        uint8_t* st32 = sSt32 + q * 2 * EPI_ST32_TILE_BYTES;
+        uint8_t* st16 = sSt16 + q * 2 * EPI_ST16_TILE_BYTES;
+        int acc = 0, ls = 0, ob = 0;
+        uint32_t pacc = 0, pls = 0;
         for (int64_t tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
             const int nt = static_cast<int>(tile % n_tiles);
             const int64_t rest = tile / n_tiles;
-            const int64_t mt = rest % p.m_tiles;
-            const int64_t b = rest / p.m_tiles;
+            const int t0 = static_cast<int>((rest % p.m_tiles) * UMMA_BLOCK_M);
+            const int b = static_cast<int>(rest / p.m_tiles);
             const int phase = nt / p.tiles_per_phase;
             const int c0 = (nt % p.tiles_per_phase) * p.n_tile;  // channel offset inside the phase
-            const int c_end = p.cout_phase;                      // valid channels of this phase
-            const int64_t t = mt * UMMA_BLOCK_M + q * 32 + lane;
-            const bool row_ok = t < p.T;
-            const int64_t row_off = (b * p.T + t) * p.N + phase * p.cout_phase;
 
             mbar_wait(&acc_full[acc], pacc);
             tc_fence_after_sync();
             const uint32_t t_addr = tmem_base + ((static_cast<uint32_t>(q) * 32u) << 16) + acc * p.n_tile;
-            for (int c = 0; c < p.n_tile; c += 16) {
-                uint32_t v[16];
-                tmem_ld_32x32b_x16(t_addr + c, v);  // warp-collective: executed by all lanes
-                tmem_ld_wait();
-                if (row_ok) {
+            for (int c = 0; c < p.n_tile; c += EPI_CHUNK) {
+                const int width = min(EPI_CHUNK, p.n_tile - c);  // 32 or 16
+                float o[32];
+                {
+                    uint32_t v[32];
+                    if (width == EPI_CHUNK) {
+                        tmem_ld_32x32b_x32(t_addr + c, v);
+                    } else {
+                        uint32_t h[16];
+                        tmem_ld_32x32b_x16(t_addr + c, h);
 #pragma unroll
-                    for (int h = 0; h < 2; ++h) {
-                        const int ch = c0 + c + 8 * h;
-                        if (ch < c_end) {  // channel counts are multiples of 8
-                            float o[8];
+                        for (int e = 0; e < 16; ++e) { v[e] = h[e]; v[16 + e] = 0u; }
+                    }
+                    tmem_ld_wait();
 #pragma unroll
-                            for (int e = 0; e < 8; ++e) o[e] = __uint_as_float(v[8 * h + e]);
-                            if (p.bias) {
-                                const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.bias + ch));
-                                const float4 b1 = __ldg(reinterpret_cast<const float4*>(p.bias + ch + 4));
-                                o[0] += b0.x; o[1] += b0.y; o[2] += b0.z; o[3] += b0.w;
-                                o[4] += b1.x; o[5] += b1.y; o[6] += b1.z; o[7] += b1.w;
-                            }
-                            if (p.residual) {
-                                const float4 r0 = *reinterpret_cast<const float4*>(p.residual + row_off + ch);
-                                const float4 r1 = *reinterpret_cast<const float4*>(p.residual + row_off + ch + 4);
-                                o[0] += r0.x; o[1] += r0.y; o[2] += r0.z; o[3] += r0.w;
-                                o[4] += r1.x; o[5] += r1.y; o[6] += r1.z; o[7] += r1.w;
-                            }
+                    for (int e = 0; e < 32; ++e) o[e] = __uint_as_float(v[e]);
+                }
+                if (c + EPI_CHUNK >= p.n_tile) {  // last TMEM read of this tile: hand the accumulator back early
+                    tc_fence_before_sync();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&acc_empty[acc]);
+                }
+                if (p.bias) {
+                    const int chb = c0 + c;
 #pragma unroll
-                            for (int e = 0; e < 8; ++e) o[e] *= p.out_scale;
-                            if (p.accum) {
-                                const float4 r0 = *reinterpret_cast<const float4*>(p.accum + row_off + ch);
-                                const float4 r1 = *reinterpret_cast<const float4*>(p.accum + row_off + ch + 4);
-                                o[0] += r0.x; o[1] += r0.y; o[2] += r0.z; o[3] += r0.w;
-                                o[4] += r1.x; o[5] += r1.y; o[6] += r1.z; o[7] += r1.w;
-                            }
-                            if (p.y_f32) {
-                                *reinterpret_cast<float4*>(p.y_f32 + row_off + ch) = make_float4(o[0], o[1], o[2], o[3]);
-                                *reinterpret_cast<float4*>(p.y_f32 + row_off + ch + 4) = make_float4(o[4], o[5], o[6], o[7]);
-                            }
-                            if (p.y_bf16) {
-                                __nv_bfloat162 h0 = __floats2bfloat162_rn(o[0], o[1]);
-                                __nv_bfloat162 h1 = __floats2bfloat162_rn(o[2], o[3]);
-                                __nv_bfloat162 h2 = __floats2bfloat162_rn(o[4], o[5]);
-                                __nv_bfloat162 h3 = __floats2bfloat162_rn(o[6], o[7]);
-                                *reinterpret_cast<uint4*>(p.y_bf16 + row_off + ch) =
-                                    make_uint4(*reinterpret_cast<unsigned int*>(&h0), *reinterpret_cast<unsigned int*>(&h1),
-                                               *reinterpret_cast<unsigned int*>(&h2), *reinterpret_cast<unsigned int*>(&h3));
-                            }
+                    for (int j = 0; j < 8; ++j) {
+                        if (chb + 4 * j < p.cout_phase) {
+                            const float4 bv = __ldg(reinterpret_cast<const float4*>(p.bias + chb + 4 * j));
+                            o[4 * j] += bv.x; o[4 * j + 1] += bv.y; o[4 * j + 2] += bv.z; o[4 * j + 3] += bv.w;
                         }
                     }
                 }
+                if (n_ld > 0) {
+                    mbar_wait(&ld_full[ls], pls);
+                    const uint8_t* ld = sLd + ls * n_ld * EPI_LD_TILE_BYTES + row * 128;
+                    if (p.has_res) {
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            const float4 rv = *reinterpret_cast<const float4*>(ld + ((j ^ sw128) << 4));
+                            o[4 * j] += rv.x; o[4 * j + 1] += rv.y; o[4 * j + 2] += rv.z; o[4 * j + 3] += rv.w;
+                        }
+                    }
+#pragma unroll
+                    for (int e = 0; e < 32; ++e) o[e] *= p.out_scale;
+                    if (p.has_acc) {
+                        const uint8_t* la = ld + p.has_res * EPI_LD_TILE_BYTES;
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            const float4 rv = *reinterpret_cast<const float4*>(la + ((j ^ sw128) << 4));
+                            o[4 * j] += rv.x; o[4 * j + 1] += rv.y; o[4 * j + 2] += rv.z; o[4 * j + 3] += rv.w;
+                        }
+                    }
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&ld_empty[ls]);
+                    if (++ls == p.ld_stages) { ls = 0; pls ^= 1; }
+                } else {
+#pragma unroll
+                    for (int e = 0; e < 32; ++e) o[e] *= p.out_scale;
+                }
+                // the smem tile written two chunks ago must have been read by its TMA store
+                if (lane == 0) tma_store_wait_read<1>();
+                __syncwarp();
+                if (p.has_y32) {
+                    uint8_t* dst = st32 + ob * EPI_ST32_TILE_BYTES + lane * 128;
+#pragma unroll
+                    for (int j = 0; j < 8; ++j)
+                        *reinterpret_cast<float4*>(dst + ((j ^ (lane & 7)) << 4)) =
+                            make_float4(o[4 * j], o[4 * j + 1], o[4 * j + 2], o[4 * j + 3]);
+                }
+                if (p.has_y16) {
+                    uint8_t* dst = st16 + ob * EPI_ST16_TILE_BYTES + lane * 64;
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        __nv_bfloat162 h0 = __floats2bfloat162_rn(o[8 * j], o[8 * j + 1]);
+                        __nv_bfloat162 h1 = __floats2bfloat162_rn(o[8 * j + 2], o[8 * j + 3]);
+                        __nv_bfloat162 h2 = __floats2bfloat162_rn(o[8 * j + 4], o[8 * j + 5]);
+                        __nv_bfloat162 h3 = __floats2bfloat162_rn(o[8 * j + 6], o[8 * j + 7]);
+                        *reinterpret_cast<uint4*>(dst + ((j ^ sw64) << 4)) =
+                            make_uint4(*reinterpret_cast<unsigned int*>(&h0), *reinterpret_cast<unsigned int*>(&h1),
+                                       *reinterpret_cast<unsigned int*>(&h2), *reinterpret_cast<unsigned int*>(&h3));
+                    }
+                }
+                fence_proxy_async_smem();
+                __syncwarp();
+                if (lane == 0) {
+                    if (p.has_y32) tma_store_4d(&map_y32, st32 + ob * EPI_ST32_TILE_BYTES, c0 + c, phase, t0 + q * 32, b);
+                    if (p.has_y16) tma_store_4d(&map_y16, st16 + ob * EPI_ST16_TILE_BYTES, c0 + c, phase, t0 + q * 32, b);
+                    tma_store_commit();
+                }
+                ob ^= 1;
             }
-            tc_fence_before_sync();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&acc_empty[acc]);
             if (++acc == 2) { acc = 0; pacc ^= 1; }
         }
+        if (lane == 0) tma_store_wait<0>();
     }
 
     tc_fence_before_sync();
@@ -253,6 +355,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
         tmem_dealloc(tmem_base, p.tmem_cols);
     }
 }
+
 
 // ------------------------------------------------------------------------------------------------------------
 // host side
@@ -299,6 +402,25 @@ static int encode_3d_bf16(CUtensorMap* map, const void* ptr, uint64_t d0, uint64
     return BVG_OK;
 }
 
+// [B,T,N] tensor viewed as [cout_phase, phases, T, B] so that column clipping is per phase.
+static int encode_io_4d(CUtensorMap* map, const void* ptr, bool bf16, uint64_t cp, uint64_t phases, uint64_t T, uint64_t B,
+                        uint32_t box_rows, const char* what) {
+    EncodeTiledFn enc = get_encode_fn();
+    BVG_REQUIRE(enc != nullptr, BVG_ERR_CUDA, "cuTensorMapEncodeTiled not available from the driver");
+    const uint64_t es = bf16 ? 2 : 4;
+    const uint64_t N = cp * phases;
+    cuuint64_t dims[4] = {cp, phases, T, B};
+    cuuint64_t strides[3] = {cp * es, N * es, T * N * es};
+    cuuint32_t box[4] = {32, 1, box_rows, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = enc(map, bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4,
+                     const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     bf16 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    BVG_REQUIRE(r == CUDA_SUCCESS, BVG_ERR_CUDA, "cuTensorMapEncodeTiled(%s) failed with CUresult %d", what, (int)r);
+    return BVG_OK;
+}
+
 // Generic launcher: plain conv (num_phases = 1) or polyphase transposed conv.
 int conv_umma_launch(const void* x, const void* w_packed, const float* bias, const float* residual, const float* accum,
                      float* y_f32, void* y_bf16, int64_t B, int64_t T, int64_t Cin, int64_t N, int64_t cout_phase,
@@ -324,30 +446,58 @@ int conv_umma_launch(const void* x, const void* w_packed, const float* bias, con
     {
         const int cp = (int)cout_phase;
         int nt = (cp + 255) / 256;
-        int tile = (int)round_up(ceil_div(cp, nt), 16);
+        // several tiles per phase: 32-column granularity so that epilogue chunks never straddle tiles
+        int tile = (int)round_up(ceil_div(cp, nt), nt > 1 ? 32 : 16);
         p.n_tile = tile;
         p.tiles_per_phase = (int)ceil_div(cp, tile);
     }
     p.m_tiles = ceil_div(T, UMMA_BLOCK_M);
     p.total_tiles = p.m_tiles * B * p.num_phases * p.tiles_per_phase;
-    p.a_rows = (int)round_up(UMMA_BLOCK_M + (taps - 1) * dil, 8);
-    p.a_stage_bytes = (uint32_t)round_up((int64_t)p.a_rows * 128, 1024);
+    const int a_rows = (int)round_up(UMMA_BLOCK_M + (taps - 1) * dil, 8);
+    p.a_stage_bytes = (uint32_t)round_up((int64_t)a_rows * 128, 1024);
     p.b_stage_bytes = (uint32_t)round_up((int64_t)p.n_tile * 128, 1024);
     uint32_t tm = 32;
     while (tm < (uint32_t)(2 * p.n_tile)) tm <<= 1;
     p.tmem_cols = tm;
-    // stages: fill ~200 KB; at least 2 A stages, B stages up to 8
-    const uint32_t budget = 200 * 1024;
-    p.a_stages = 2;
-    int bs = (int)((budget - p.a_stages * p.a_stage_bytes) / p.b_stage_bytes);
-    if (bs > UMMA_MAX_STAGES) bs = UMMA_MAX_STAGES;
-    BVG_REQUIRE(bs >= 2, BVG_ERR_UNSUPPORTED, "conv_umma: tile does not fit shared memory");
-    p.b_stages = bs;
-    if ((uint32_t)(3 * p.a_stage_bytes + p.b_stages * p.b_stage_bytes) <= budget) p.a_stages = 3;
-    const SmemLayout lay = smem_layout(p);
-    const uint32_t smem_bytes = lay.total + 1024;
+    p.has_res = residual != nullptr; p.has_acc = accum != nullptr;
+    p.has_y32 = y_f32 != nullptr; p.has_y16 = y_bf16 != nullptr;
+    const int n_ld = p.has_res + p.has_acc;
+    BVG_REQUIRE(reinterpret_cast<uintptr_t>(residual) % 16 == 0 && reinterpret_cast<uintptr_t>(accum) % 16 == 0 &&
+                    reinterpret_cast<uintptr_t>(y_f32) % 16 == 0 && reinterpret_cast<uintptr_t>(y_bf16) % 16 == 0,
+                BVG_ERR_INVALID, "conv_umma: residual / accum / outputs must be 16-byte aligned");
+    // shared memory plan: 227 KB - alignment slack - barriers - epilogue tiles is what the operand pipelines get
+    const int k_blocks = (int)ceil_div(Cin, UMMA_BLOCK_K);
+    const int64_t w_all = (int64_t)p.num_phases * p.tiles_per_phase * k_blocks * taps * p.b_stage_bytes;
+    const uint32_t st_bytes = (p.has_y32 ? 8 * EPI_ST32_TILE_BYTES : 0) + (p.has_y16 ? 8 * EPI_ST16_TILE_BYTES : 0);
+    const uint32_t fixed = 1024 + 1024 + st_bytes;
+    for (p.ld_stages = (n_ld ? 2 : 0);; --p.ld_stages) {
+        const uint32_t budget = 227 * 1024 - fixed - p.ld_stages * n_ld * EPI_LD_TILE_BYTES;
+        if (w_all <= 112 * 1024 && (int64_t)budget - w_all >= 2 * (int64_t)p.a_stage_bytes) {
+            // weight-stationary: all weight tiles resident, deep activation ring
+            p.stationary = 1;
+            p.w_bytes = (uint32_t)w_all;
+            p.b_stages = 0;
+            int as = (int)((budget - p.w_bytes) / p.a_stage_bytes);
+            p.a_stages = as > UMMA_MAX_STAGES ? UMMA_MAX_STAGES : as;
+            break;
+        }
+        p.stationary = 0;
+        p.w_bytes = 0;
+        p.a_stages = 2;
+        int bs = ((int64_t)budget > 2 * (int64_t)p.a_stage_bytes) ? (int)((budget - 2 * p.a_stage_bytes) / p.b_stage_bytes) : 0;
+        if (bs > UMMA_MAX_STAGES) bs = UMMA_MAX_STAGES;
+        p.b_stages = bs;
+        if (bs >= 3 || (bs >= 2 && p.ld_stages <= 1)) {
+            if ((uint32_t)(3 * p.a_stage_bytes + p.b_stages * p.b_stage_bytes) <= budget) p.a_stages = 3;
+            break;
+        }
+        BVG_REQUIRE(p.ld_stages > 1, BVG_ERR_UNSUPPORTED, "conv_umma: tile does not fit shared memory");
+    }
+    const uint32_t smem_bytes = p.a_stages * p.a_stage_bytes + (p.stationary ? p.w_bytes : p.b_stages * p.b_stage_bytes) +
+                                p.ld_stages * n_ld * EPI_LD_TILE_BYTES + st_bytes + 1024 + 1024;
+    BVG_REQUIRE(smem_bytes <= 227 * 1024, BVG_ERR_UNSUPPORTED, "conv_umma: %u bytes of shared memory needed", smem_bytes);
 
-    CUtensorMap map_x, map_w;
+    CUtensorMap map_x, map_w, map_res, map_acc, map_y32, map_y16;
     // the A box is a_stage_bytes/128 rows so that expect_tx matches the bytes TMA writes
     const uint32_t a_box_rows = p.a_stage_bytes / 128;
     BVG_REQUIRE(a_box_rows <= 256, BVG_ERR_UNSUPPORTED, "conv_umma: halo tile of %u rows exceeds the TMA box limit", a_box_rows);
@@ -368,7 +518,12 @@ int conv_umma_launch(const void* x, const void* w_packed, const float* bias, con
     }
     const int sms = device_sm_count();
     const int grid = (int)(p.total_tiles < sms ? p.total_tiles : sms);
-    conv_umma_kernel<<<grid, UMMA_THREADS, smem_bytes, st>>>(map_x, map_w, p);
+    map_res = map_acc = map_y32 = map_y16 = map_x;  // placeholders for unused maps
+    if (p.has_res && (rc = encode_io_4d(&map_res, residual, false, cout_phase, num_phases, T, B, 128, "residual")) != BVG_OK) return rc;
+    if (p.has_acc && (rc = encode_io_4d(&map_acc, accum, false, cout_phase, num_phases, T, B, 128, "accum")) != BVG_OK) return rc;
+    if (p.has_y32 && (rc = encode_io_4d(&map_y32, y_f32, false, cout_phase, num_phases, T, B, 32, "y_f32")) != BVG_OK) return rc;
+    if (p.has_y16 && (rc = encode_io_4d(&map_y16, y_bf16, true, cout_phase, num_phases, T, B, 32, "y_bf16")) != BVG_OK) return rc;
+    conv_umma_kernel<<<grid, UMMA_THREADS, smem_bytes, st>>>(map_x, map_w, map_res, map_acc, map_y32, map_y16, p);
     BVG_LAUNCH_CHECK("conv_umma_kernel");
     return BVG_OK;
 }
