@@ -164,44 +164,56 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
     } else if (warp == 1) {
         // ------------------------------ UMMA issuer ------------------------------
         if (lane == 0) {
+            // Single-thread issue loop: everything loop-invariant is hoisted and the shared-memory descriptors are
+            // advanced by integer adds (start-address field = byte address >> 4), so one UMMA costs a few instructions.
             const uint32_t idesc = umma_idesc_bf16_f32(UMMA_BLOCK_M, p.n_tile);
+            const uint64_t desc_hi = umma_desc_sw128_kmajor(0);           // layout/SBO/version bits, address 0
+            const uint32_t tap_step = static_cast<uint32_t>(p.dil) * 8u;  // dil rows * 128 B >> 4
+            const uint32_t b_step = p.b_stage_bytes >> 4;
+            const int taps = p.taps;
+            const int a_stages = p.a_stages, b_stages = p.b_stages;
+            const bool stationary = p.stationary != 0;
+            const int last_steps = ((p.Cin - (k_blocks - 1) * UMMA_BLOCK_K) + 15) / 16;
+            const uint32_t sA_d = smem_u32(sA) >> 4, sB_d = smem_u32(sB) >> 4;
+            const uint32_t a_stage_d = p.a_stage_bytes >> 4;
             int sa = 0, sb = 0, acc = 0;
             uint32_t pa = 0, pb = 0, pacc = 0;
-            if (p.stationary) mbar_wait(&b_full[0], 0);
+            if (stationary) mbar_wait(&b_full[0], 0);
             for (int64_t tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
                 const int nt = static_cast<int>(tile % n_tiles);
                 mbar_wait(&acc_empty[acc], pacc ^ 1);
                 tc_fence_after_sync();
                 const uint32_t d_tmem = tmem_base + acc * p.n_tile;
                 uint32_t accumulate = 0;
+                uint32_t w_d = sB_d + static_cast<uint32_t>(nt * k_blocks * taps) * b_step;  // stationary weight cursor
                 for (int kb = 0; kb < k_blocks; ++kb) {
-                    const int k_rem = p.Cin - kb * UMMA_BLOCK_K;
-                    const int k_steps = (min(k_rem, UMMA_BLOCK_K) + 15) / 16;
+                    const int k_steps = (kb + 1 == k_blocks) ? last_steps : 4;
                     mbar_wait(&a_full[sa], pa);
                     tc_fence_after_sync();
-                    const uint32_t a_addr = smem_u32(sA + sa * p.a_stage_bytes);
-                    for (int j = 0; j < p.taps; ++j) {
-                        uint32_t b_addr;
-                        if (p.stationary) {
-                            b_addr = smem_u32(sB + ((nt * k_blocks + kb) * p.taps + j) * p.b_stage_bytes);
+                    uint64_t a_desc = desc_hi | static_cast<uint64_t>(sA_d + sa * a_stage_d);
+                    for (int j = 0; j < taps; ++j) {
+                        uint64_t b_desc;
+                        if (stationary) {
+                            b_desc = desc_hi | static_cast<uint64_t>(w_d);
+                            w_d += b_step;
                         } else {
                             mbar_wait(&b_full[sb], pb);
                             tc_fence_after_sync();
-                            b_addr = smem_u32(sB + sb * p.b_stage_bytes);
+                            b_desc = desc_hi | static_cast<uint64_t>(sB_d + sb * b_step);
                         }
-                        const uint32_t a_tap = a_addr + static_cast<uint32_t>(j * p.dil) * 128u;
-                        for (int ks = 0; ks < k_steps; ++ks) {
-                            umma_f16(d_tmem, umma_desc_sw128_kmajor(a_tap + ks * 32), umma_desc_sw128_kmajor(b_addr + ks * 32),
-                                     idesc, accumulate);
-                            accumulate = 1;
-                        }
-                        if (!p.stationary) {
+                        umma_f16(d_tmem, a_desc, b_desc, idesc, accumulate);
+                        accumulate = 1;
+                        if (k_steps > 1) umma_f16(d_tmem, a_desc + 2, b_desc + 2, idesc, 1);
+                        if (k_steps > 2) umma_f16(d_tmem, a_desc + 4, b_desc + 4, idesc, 1);
+                        if (k_steps > 3) umma_f16(d_tmem, a_desc + 6, b_desc + 6, idesc, 1);
+                        a_desc += tap_step;
+                        if (!stationary) {
                             umma_commit(&b_empty[sb]);
-                            if (++sb == p.b_stages) { sb = 0; pb ^= 1; }
+                            if (++sb == b_stages) { sb = 0; pb ^= 1; }
                         }
                     }
                     umma_commit(&a_empty[sa]);
-                    if (++sa == p.a_stages) { sa = 0; pa ^= 1; }
+                    if (++sa == a_stages) { sa = 0; pa ^= 1; }
                 }
                 umma_commit(&acc_full[acc]);
                 if (++acc == 2) { acc = 0; pacc ^= 1; }
@@ -483,14 +495,16 @@ int conv_umma_launch(const void* x, const void* w_packed, const float* bias, con
         }
         p.stationary = 0;
         p.w_bytes = 0;
-        p.a_stages = 2;
-        int bs = ((int64_t)budget > 2 * (int64_t)p.a_stage_bytes) ? (int)((budget - 2 * p.a_stage_bytes) / p.b_stage_bytes) : 0;
+        // prefer 3 activation stages when at least 4 weight stages still fit
+        p.a_stages = 3;
+        int bs = ((int64_t)budget > 3 * (int64_t)p.a_stage_bytes) ? (int)((budget - 3 * p.a_stage_bytes) / p.b_stage_bytes) : 0;
+        if (bs < 4) {
+            p.a_stages = 2;
+            bs = ((int64_t)budget > 2 * (int64_t)p.a_stage_bytes) ? (int)((budget - 2 * p.a_stage_bytes) / p.b_stage_bytes) : 0;
+        }
         if (bs > UMMA_MAX_STAGES) bs = UMMA_MAX_STAGES;
         p.b_stages = bs;
-        if (bs >= 3 || (bs >= 2 && p.ld_stages <= 1)) {
-            if ((uint32_t)(3 * p.a_stage_bytes + p.b_stages * p.b_stage_bytes) <= budget) p.a_stages = 3;
-            break;
-        }
+        if (bs >= 3 || (bs >= 2 && p.ld_stages <= 1)) break;
         BVG_REQUIRE(p.ld_stages > 1, BVG_ERR_UNSUPPORTED, "conv_umma: tile does not fit shared memory");
     }
     const uint32_t smem_bytes = p.a_stages * p.a_stage_bytes + (p.stationary ? p.w_bytes : p.b_stages * p.b_stage_bytes) +
