@@ -174,7 +174,9 @@ __device__ __forceinline__ void act1d_nlc_segment(const TIn* __restrict__ xb, TO
         return PairIO<TIn>::load(xrel + (int64_t)rel * C);
     };
     // x window: x[m+j], j=-3..3, lives in xw[(s+j+3)%7] at step s of a 7-step body; pair m in ve/vo[s].
-    float2 xw[7], ve[7], vo[7], cur[7], nxt[7];
+    // Loads run two 7-row bodies (~14 rows, > 1 us of work per warp) ahead of their use: global latency is hidden by
+    // the register prefetch queue cur <- nxt <- nxt2 rather than by occupancy (2 CTAs/SM at ~110 registers).
+    float2 xw[7], ve[7], vo[7], cur[7], nxt[7], nxt2[7];
     float2 vlast = splat(0.f);
 #pragma unroll
     for (int j = 0; j < 6; ++j) xw[j] = ldx(j);
@@ -184,19 +186,19 @@ __device__ __forceinline__ void act1d_nlc_segment(const TIn* __restrict__ xb, TO
         ve[s] = vo[s] = splat(0.f);
     }
     const int nbody = (L + 6) / 7;
-    if (nbody > 1) {
 #pragma unroll
-        for (int s = 0; s < 7; ++s) nxt[s] = ldx(13 + s);
-    }
+    for (int s = 0; s < 7; ++s) nxt[s] = nbody > 1 ? ldx(13 + s) : splat(0.f);
+#pragma unroll
+    for (int s = 0; s < 7; ++s) nxt2[s] = nbody > 2 ? ldx(20 + s) : splat(0.f);
     act1d_nlc_body<TOut, PRECISE, EDGE, true>(xw, ve, vo, cur, vlast, coef, e, 0, yrel, C);
 #pragma unroll 1
     for (int body = 1; body < nbody; ++body) {
         const int g0 = 7 * body;
 #pragma unroll
-        for (int s = 0; s < 7; ++s) cur[s] = nxt[s];
-        if (body + 1 < nbody) {
+        for (int s = 0; s < 7; ++s) { cur[s] = nxt[s]; nxt[s] = nxt2[s]; }
+        if (body + 2 < nbody) {
 #pragma unroll
-            for (int s = 0; s < 7; ++s) nxt[s] = ldx(g0 + 13 + s);
+            for (int s = 0; s < 7; ++s) nxt2[s] = ldx(g0 + 20 + s);
         }
         act1d_nlc_body<TOut, PRECISE, EDGE, false>(xw, ve, vo, cur, vlast, coef, e, g0, yrel, C);
     }

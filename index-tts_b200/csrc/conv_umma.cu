@@ -66,7 +66,7 @@ struct ConvUmmaParams {
     // epilogue I/O is all TMA: residual / accum chunks are prefetched by a loader warp, outputs leave through
     // per-warp swizzled smem tiles and bulk tensor stores
     int has_res, has_acc, has_y32, has_y16;
-    int ld_stages;     // residual/accum chunk ring depth (1 or 2)
+    int ld_stages;     // residual/accum chunk ring depth (<= UMMA_MAX_STAGES)
     float out_scale;
 };
 
@@ -92,9 +92,9 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
     uint64_t* b_empty = bars + 3 * UMMA_MAX_STAGES;
     uint64_t* acc_full = bars + 4 * UMMA_MAX_STAGES;  // [2]
     uint64_t* acc_empty = acc_full + 2;               // [2]
-    uint64_t* ld_full = acc_empty + 2;                // [2]
-    uint64_t* ld_empty = ld_full + 2;                 // [2]
-    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(ld_empty + 2);
+    uint64_t* ld_full = acc_empty + 2;                // [UMMA_MAX_STAGES]
+    uint64_t* ld_empty = ld_full + UMMA_MAX_STAGES;   // [UMMA_MAX_STAGES]
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(ld_empty + UMMA_MAX_STAGES);
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -105,11 +105,9 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
         for (int i = 0; i < UMMA_MAX_STAGES; ++i) {
             mbar_init(&a_full[i], 1); mbar_init(&a_empty[i], 1);
             mbar_init(&b_full[i], 1); mbar_init(&b_empty[i], 1);
-        }
-        for (int i = 0; i < 2; ++i) {
-            mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 4);
             mbar_init(&ld_full[i], 1); mbar_init(&ld_empty[i], 4);
         }
+        for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 4); }
         fence_barrier_init();
     }
     if (warp == 1) tmem_alloc(tmem_ptr, p.tmem_cols);
@@ -123,47 +121,53 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
 
     if (warp == 0) {
         // ------------------------------ TMA producer ------------------------------
-        if (lane == 0) {
-            if (p.stationary) {
-                mbar_arrive_expect_tx(&b_full[0], p.w_bytes);
-                for (int nt = 0; nt < n_tiles; ++nt) {
-                    const int n0 = (nt / p.tiles_per_phase) * p.cout_phase + (nt % p.tiles_per_phase) * p.n_tile;
-                    for (int kb = 0; kb < k_blocks; ++kb)
-                        for (int j = 0; j < p.taps; ++j)
+        // The whole warp runs the control flow (so every value stays warp-uniform and lives in uniform registers);
+        // one elected lane issues the TMA operations.
+        if (p.stationary) {
+            if (elect_one()) mbar_arrive_expect_tx(&b_full[0], p.w_bytes);
+            __syncwarp();
+            for (int nt = 0; nt < n_tiles; ++nt) {
+                const int n0 = (nt / p.tiles_per_phase) * p.cout_phase + (nt % p.tiles_per_phase) * p.n_tile;
+                for (int kb = 0; kb < k_blocks; ++kb)
+                    for (int j = 0; j < p.taps; ++j)
+                        if (elect_one())
                             tma_load_3d_hint(sB + ((nt * k_blocks + kb) * p.taps + j) * p.b_stage_bytes, &map_w, &b_full[0],
                                              kb * UMMA_BLOCK_K, n0, j, kPolicyEvictLast);
-                }
             }
-            int sa = 0, sb = 0;
-            uint32_t pa = 0, pb = 0;
-            for (int64_t tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
-                const int nt = static_cast<int>(tile % n_tiles);
-                const int64_t rest = tile / n_tiles;
-                const int64_t mt = rest % p.m_tiles;
-                const int b = static_cast<int>(rest / p.m_tiles);
-                const int phase = nt / p.tiles_per_phase;
-                const int n0 = phase * p.cout_phase + (nt % p.tiles_per_phase) * p.n_tile;
-                const int row0 = static_cast<int>(mt * UMMA_BLOCK_M) + p.tap_base[phase];
-                for (int kb = 0; kb < k_blocks; ++kb) {
-                    mbar_wait(&a_empty[sa], pa ^ 1);
+        }
+        int sa = 0, sb = 0;
+        uint32_t pa = 0, pb = 0;
+        for (int64_t tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+            const int nt = static_cast<int>(tile % n_tiles);
+            const int64_t rest = tile / n_tiles;
+            const int64_t mt = rest % p.m_tiles;
+            const int b = static_cast<int>(rest / p.m_tiles);
+            const int phase = nt / p.tiles_per_phase;
+            const int n0 = phase * p.cout_phase + (nt % p.tiles_per_phase) * p.n_tile;
+            const int row0 = static_cast<int>(mt * UMMA_BLOCK_M) + p.tap_base[phase];
+            for (int kb = 0; kb < k_blocks; ++kb) {
+                mbar_wait(&a_empty[sa], pa ^ 1);
+                if (elect_one()) {
                     mbar_arrive_expect_tx(&a_full[sa], p.a_stage_bytes);
                     tma_load_3d(sA + sa * p.a_stage_bytes, &map_x, &a_full[sa], kb * UMMA_BLOCK_K, row0, b);
-                    if (++sa == p.a_stages) { sa = 0; pa ^= 1; }
-                    if (!p.stationary) {
-                        for (int j = 0; j < p.taps; ++j) {
-                            mbar_wait(&b_empty[sb], pb ^ 1);
+                }
+                if (++sa == p.a_stages) { sa = 0; pa ^= 1; }
+                if (!p.stationary) {
+                    for (int j = 0; j < p.taps; ++j) {
+                        mbar_wait(&b_empty[sb], pb ^ 1);
+                        if (elect_one()) {
                             mbar_arrive_expect_tx(&b_full[sb], p.b_stage_bytes);
                             tma_load_3d_hint(sB + sb * p.b_stage_bytes, &map_w, &b_full[sb], kb * UMMA_BLOCK_K, n0, j,
                                              kPolicyEvictLast);
-                            if (++sb == p.b_stages) { sb = 0; pb ^= 1; }
                         }
+                        if (++sb == p.b_stages) { sb = 0; pb ^= 1; }
                     }
                 }
             }
         }
     } else if (warp == 1) {
         // ------------------------------ UMMA issuer ------------------------------
-        if (lane == 0) {
+        {
             // Single-thread issue loop: everything loop-invariant is hoisted and the shared-memory descriptors are
             // advanced by integer adds (start-address field = byte address >> 4), so one UMMA costs a few instructions.
             const uint32_t idesc = umma_idesc_bf16_f32(UMMA_BLOCK_M, p.n_tile);
@@ -201,27 +205,29 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                             tc_fence_after_sync();
                             b_desc = desc_hi | static_cast<uint64_t>(sB_d + sb * b_step);
                         }
-                        umma_f16(d_tmem, a_desc, b_desc, idesc, accumulate);
+                        if (elect_one()) {
+                            umma_f16(d_tmem, a_desc, b_desc, idesc, accumulate);
+                            if (k_steps > 1) umma_f16(d_tmem, a_desc + 2, b_desc + 2, idesc, 1);
+                            if (k_steps > 2) umma_f16(d_tmem, a_desc + 4, b_desc + 4, idesc, 1);
+                            if (k_steps > 3) umma_f16(d_tmem, a_desc + 6, b_desc + 6, idesc, 1);
+                            if (!stationary) umma_commit(&b_empty[sb]);
+                        }
                         accumulate = 1;
-                        if (k_steps > 1) umma_f16(d_tmem, a_desc + 2, b_desc + 2, idesc, 1);
-                        if (k_steps > 2) umma_f16(d_tmem, a_desc + 4, b_desc + 4, idesc, 1);
-                        if (k_steps > 3) umma_f16(d_tmem, a_desc + 6, b_desc + 6, idesc, 1);
                         a_desc += tap_step;
                         if (!stationary) {
-                            umma_commit(&b_empty[sb]);
                             if (++sb == b_stages) { sb = 0; pb ^= 1; }
                         }
                     }
-                    umma_commit(&a_empty[sa]);
+                    if (elect_one()) umma_commit(&a_empty[sa]);
                     if (++sa == a_stages) { sa = 0; pa ^= 1; }
                 }
-                umma_commit(&acc_full[acc]);
+                if (elect_one()) umma_commit(&acc_full[acc]);
                 if (++acc == 2) { acc = 0; pacc ^= 1; }
             }
         }
     } else if (warp == 6) {
         // ------------------------------ residual / accum chunk loader ------------------------------
-        if (lane == 0 && n_ld > 0) {
+        if (n_ld > 0) {
             int s = 0;
             uint32_t ps = 0;
             for (int64_t tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
@@ -233,10 +239,13 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                 const int c0 = (nt % p.tiles_per_phase) * p.n_tile;
                 for (int c = 0; c < p.n_tile; c += EPI_CHUNK) {
                     mbar_wait(&ld_empty[s], ps ^ 1);
-                    mbar_arrive_expect_tx(&ld_full[s], n_ld * EPI_LD_TILE_BYTES);
-                    uint8_t* dst = sLd + s * n_ld * EPI_LD_TILE_BYTES;
-                    if (p.has_res) tma_load_4d(dst, &map_res, &ld_full[s], c0 + c, phase, t0, b);
-                    if (p.has_acc) tma_load_4d(dst + p.has_res * EPI_LD_TILE_BYTES, &map_acc, &ld_full[s], c0 + c, phase, t0, b);
+                    if (elect_one()) {
+                        mbar_arrive_expect_tx(&ld_full[s], n_ld * EPI_LD_TILE_BYTES);
+                        uint8_t* dst = sLd + s * n_ld * EPI_LD_TILE_BYTES;
+                        if (p.has_res) tma_load_4d(dst, &map_res, &ld_full[s], c0 + c, phase, t0, b);
+                        if (p.has_acc)
+                            tma_load_4d(dst + p.has_res * EPI_LD_TILE_BYTES, &map_acc, &ld_full[s], c0 + c, phase, t0, b);
+                    }
                     if (++s == p.ld_stages) { s = 0; ps ^= 1; }
                 }
             }
@@ -482,31 +491,37 @@ int conv_umma_launch(const void* x, const void* w_packed, const float* bias, con
     const int64_t w_all = (int64_t)p.num_phases * p.tiles_per_phase * k_blocks * taps * p.b_stage_bytes;
     const uint32_t st_bytes = (p.has_y32 ? 8 * EPI_ST32_TILE_BYTES : 0) + (p.has_y16 ? 8 * EPI_ST16_TILE_BYTES : 0);
     const uint32_t fixed = 1024 + 1024 + st_bytes;
-    for (p.ld_stages = (n_ld ? 2 : 0);; --p.ld_stages) {
-        const uint32_t budget = 227 * 1024 - fixed - p.ld_stages * n_ld * EPI_LD_TILE_BYTES;
-        if (w_all <= 112 * 1024 && (int64_t)budget - w_all >= 2 * (int64_t)p.a_stage_bytes) {
-            // weight-stationary: all weight tiles resident, deep activation ring
-            p.stationary = 1;
-            p.w_bytes = (uint32_t)w_all;
-            p.b_stages = 0;
-            int as = (int)((budget - p.w_bytes) / p.a_stage_bytes);
-            p.a_stages = as > UMMA_MAX_STAGES ? UMMA_MAX_STAGES : as;
-            break;
+    const int64_t avail = 227 * 1024 - (int64_t)fixed;
+    const int64_t ld_stage_bytes = (int64_t)n_ld * EPI_LD_TILE_BYTES;
+    bool planned = false;
+    if (w_all <= 112 * 1024 && avail - w_all >= 2 * (int64_t)p.a_stage_bytes + ld_stage_bytes) {
+        // weight-stationary: all weight tiles resident; the rest is split between a deep activation ring and a deep
+        // residual/accum ring (both hide DRAM latency, a tile is only ~1 us of work here)
+        p.stationary = 1;
+        p.w_bytes = (uint32_t)w_all;
+        p.b_stages = 0;
+        const int64_t rem = avail - w_all;
+        for (int ld = n_ld ? UMMA_MAX_STAGES : 0;; --ld) {
+            int64_t as = (rem - ld * ld_stage_bytes) / p.a_stage_bytes;
+            if (as > UMMA_MAX_STAGES) as = UMMA_MAX_STAGES;
+            if (as >= 4 || (ld <= 1 && as >= 2)) { p.a_stages = (int)as; p.ld_stages = ld; planned = true; break; }
+            if (ld <= 1) break;
         }
+    }
+    if (!planned) {
         p.stationary = 0;
         p.w_bytes = 0;
-        // prefer 3 activation stages when at least 4 weight stages still fit
-        p.a_stages = 3;
-        int bs = ((int64_t)budget > 3 * (int64_t)p.a_stage_bytes) ? (int)((budget - 3 * p.a_stage_bytes) / p.b_stage_bytes) : 0;
-        if (bs < 4) {
-            p.a_stages = 2;
-            bs = ((int64_t)budget > 2 * (int64_t)p.a_stage_bytes) ? (int)((budget - 2 * p.a_stage_bytes) / p.b_stage_bytes) : 0;
+        for (int ld = n_ld ? 4 : 0;; --ld) {
+            const int64_t rem = avail - ld * ld_stage_bytes;
+            int as = 3;
+            int64_t bs = (rem - 3 * (int64_t)p.a_stage_bytes) / p.b_stage_bytes;
+            if (bs < 4) { as = 2; bs = (rem - 2 * (int64_t)p.a_stage_bytes) / p.b_stage_bytes; }
+            if (bs > UMMA_MAX_STAGES) bs = UMMA_MAX_STAGES;
+            if (bs >= 4 || (ld <= 1 && bs >= 2)) { p.a_stages = as; p.b_stages = (int)bs; p.ld_stages = ld; planned = true; break; }
+            if (ld <= 1) break;
         }
-        if (bs > UMMA_MAX_STAGES) bs = UMMA_MAX_STAGES;
-        p.b_stages = bs;
-        if (bs >= 3 || (bs >= 2 && p.ld_stages <= 1)) break;
-        BVG_REQUIRE(p.ld_stages > 1, BVG_ERR_UNSUPPORTED, "conv_umma: tile does not fit shared memory");
     }
+    BVG_REQUIRE(planned, BVG_ERR_UNSUPPORTED, "conv_umma: tile does not fit shared memory");
     const uint32_t smem_bytes = p.a_stages * p.a_stage_bytes + (p.stationary ? p.w_bytes : p.b_stages * p.b_stage_bytes) +
                                 p.ld_stages * n_ld * EPI_LD_TILE_BYTES + st_bytes + 1024 + 1024;
     BVG_REQUIRE(smem_bytes <= 227 * 1024, BVG_ERR_UNSUPPORTED, "conv_umma: %u bytes of shared memory needed", smem_bytes);
