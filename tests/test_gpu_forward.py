@@ -43,7 +43,13 @@ def test_mini_generator_golden(golden_dir, form):
         m.remove_weight_norm()
         with torch.no_grad():
             wav2 = m(mel).cpu().numpy()
-        assert snr_db(wav, wav2) > 60
+        # torch's fold and bvg_fold_weight_norm differ in the last ulp, which moves some bf16 weight roundings: the two
+        # bf16 runs are equally far from the reference but not identical -- judge each against the reference.
+        _check_bf16(g["wav64"], wav2, f"mini/{form} after remove_weight_norm")
+        m.set_precision("fp32")
+        with torch.no_grad():
+            wav3 = m(mel).cpu().numpy()
+        _check_fp32(g["wav64"], wav3, f"mini/{form} after remove_weight_norm")
 
 
 @pytest.fixture(scope="module")
