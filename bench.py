@@ -228,6 +228,26 @@ def main():
         step_e2e()
     ms_e2e = timed(step_e2e, args.steps)
 
+    # ---- long-form leg (BASELINE.json configs[3]): one 120 s mel split along time over the N ranks with the
+    # 38-frame receptive-field halo, core pieces P2P-sent (NCCL send/recv) into rank 0's output buffer.  No collective
+    # on the data path; the all_reduce(MAX) below only reduces the timing.
+    from index_tts_b200 import sharding
+    long_T = 10336
+    mel_long = torch.randn(1, NUM_MELS, long_T, generator=torch.Generator().manual_seed(2)).to(dev)
+    fwd = lambda m: model(m)
+
+    def step_long():
+        with torch.no_grad():
+            return sharding.forward_time_sharded(fwd, mel_long, HOP, dst=0)
+
+    for _ in range(2):
+        step_long()
+    ms_long = timed(step_long, 3)
+    long_form = {"workload": "cfg4: one 120 s mel (80x10336) time-sharded over the ranks, 38-frame halo, P2P stitch to rank 0",
+                 "value": (long_T * HOP / SR) / (ms_long * 1e-3), "unit": "audio-s/s", "ms": ms_long, "n_gpus": world,
+                 "redundant_frames_per_rank": 0 if world == 1 else 2 * sharding.RECEPTIVE_HALO_FRAMES,
+                 "exchange": "none" if world == 1 else "NCCL send/recv of core waveform pieces (no collective)"}
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -294,6 +314,7 @@ def main():
                                "frac": roof_ms_total / meas_ms_total if meas_ms_total > 0 else None,
                                "definition": "sum over layers of max(FLOPs/bf16 sustained peak, algorithmic bytes/HBM peak) / sum of CUDA-event kernel times"},
         "kernels": kernels,
+        "long_form": long_form,
         "cpu_baseline": cpu,
     }
     print(json.dumps(line))
