@@ -19,6 +19,9 @@
 //    consecutive outputs from registers and writes them with 128-bit stores.
 #include "bvg_common.cuh"
 #include "sm100_ptx.cuh"
+#include "tma_host.cuh"
+
+#include <cstdlib>
 
 namespace bvg {
 
@@ -226,6 +229,172 @@ act1d_nlc_kernel(const TIn* __restrict__ x, TOut* __restrict__ y, const float* _
 }
 
 // ------------------------------------------------------------------------------------------------------------
+// channels-last kernel, TMA-pipelined (the one bvg_forward uses)
+// ------------------------------------------------------------------------------------------------------------
+// A work unit is (batch item, chunk of CC channels, group of `nsegs` consecutive time segments of L rows).  The 256
+// compute threads of a CTA map to (channel pair, segment); each marches along its segment with the same register
+// sliding windows as above, but its input rows arrive through a ring of shared-memory "slabs": slab q of a unit holds
+// rows t0_s - 7 + 7q .. +6 of EVERY segment s of the group (one TMA box [CC x 7 rows] per segment, all completing on
+// one mbarrier).  A producer warp keeps the ring full, so the compute warps never wait on global memory: they read 7
+// rows into registers, hand the slab straight back, and spend the rest of the body on FFMA2/MUFU work.  TMA
+// zero-fills rows outside [0,T); the sequence ends (replicate padding of x and of the activated 2x signal) are fixed
+// up in registers on the EDGE path.
+constexpr int ACT_TMA_COMPUTE = 256;
+constexpr int ACT_TMA_THREADS = ACT_TMA_COMPUTE + 32;
+constexpr int ACT_TMA_MAX_STAGES = 8;
+
+struct ActTmaParams {
+    int64_t T;
+    int C, CC, P, nsegs, L, nbody, n_cchunks;
+    uint32_t groups_per_b, n_units;
+    int stages;
+    uint32_t seg_stride;   // bytes between the segments of one slab (multiple of 128)
+    uint32_t row_bytes;    // CC * sizeof(TIn)
+    uint32_t stage_bytes;  // nsegs * seg_stride
+    uint32_t tx_bytes;     // nsegs * 7 * row_bytes
+};
+
+template <typename T>
+struct SmemPair;
+template <>
+struct SmemPair<float> {
+    static __device__ __forceinline__ float2 load(const uint8_t* p) { return *reinterpret_cast<const float2*>(p); }
+};
+template <>
+struct SmemPair<__nv_bfloat16> {
+    static __device__ __forceinline__ float2 load(const uint8_t* p) {
+        const unsigned int raw = *reinterpret_cast<const unsigned int*>(p);
+        return make_float2(__uint_as_float(raw << 16), __uint_as_float(raw & 0xffff0000u));
+    }
+};
+
+template <typename TIn, typename TOut, bool PRECISE>
+__global__ void __launch_bounds__(ACT_TMA_THREADS, 2)
+act1d_nlc_tma_kernel(const __grid_constant__ CUtensorMap map_x, TOut* __restrict__ y, const float* __restrict__ alpha,
+                     const float* __restrict__ beta, const __grid_constant__ ActTmaParams p) {
+    extern __shared__ uint8_t act_smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(act_smem_raw) + 127) & ~uintptr_t(127));
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem + p.stages * p.stage_bytes);
+    uint64_t* empty = full + ACT_TMA_MAX_STAGES;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) {
+        tma_prefetch_desc(&map_x);
+        for (int i = 0; i < p.stages; ++i) {
+            mbar_init(&full[i], 1);
+            mbar_init(&empty[i], ACT_TMA_COMPUTE / 32);
+        }
+        fence_barrier_init();
+    }
+    __syncthreads();
+    const int n_slabs = p.nbody + 1;
+    int st = 0;
+    uint32_t ph = 0;
+
+    if (warp == ACT_TMA_COMPUTE / 32) {
+        // ------------------------------ TMA producer ------------------------------
+        for (uint32_t unit = blockIdx.x; unit < p.n_units; unit += gridDim.x) {
+            const uint32_t cch = unit % p.n_cchunks;
+            const uint32_t rest = unit / p.n_cchunks;
+            const uint32_t b = rest / p.groups_per_b;
+            const uint32_t g = rest - b * p.groups_per_b;
+            const int row_base = static_cast<int>(g) * p.nsegs * p.L - 7;
+            for (int q = 0; q < n_slabs; ++q) {
+                mbar_wait(&empty[st], ph ^ 1);
+                if (lane == 0) mbar_arrive_expect_tx(&full[st], p.tx_bytes);
+                __syncwarp();
+                uint8_t* dst = smem + st * p.stage_bytes;
+                for (int s = lane; s < p.nsegs; s += 32)
+                    tma_load_3d(dst + s * p.seg_stride, &map_x, &full[st], static_cast<int>(cch) * p.CC,
+                                row_base + s * p.L + 7 * q, static_cast<int>(b));
+                if (++st == p.stages) { st = 0; ph ^= 1; }
+            }
+        }
+        return;
+    }
+
+    // ------------------------------ compute warps ------------------------------
+    const int tid = threadIdx.x;
+    const int seg_raw = tid / p.P;
+    const bool lane_used = seg_raw < p.nsegs;
+    const int seg = lane_used ? seg_raw : 0;
+    const int pair = tid - seg_raw * p.P;
+    const uint32_t my_off = seg * p.seg_stride + pair * 2u * static_cast<uint32_t>(sizeof(TIn));
+    const int L = p.L, C = p.C;
+    const int64_t T = p.T;
+
+    for (uint32_t unit = blockIdx.x; unit < p.n_units; unit += gridDim.x) {
+        const uint32_t cch = unit % p.n_cchunks;
+        const uint32_t rest = unit / p.n_cchunks;
+        const uint32_t b = rest / p.groups_per_b;
+        const uint32_t g = rest - b * p.groups_per_b;
+        const int64_t t0 = (static_cast<int64_t>(g) * p.nsegs + seg) * L;
+        const bool active = lane_used && t0 < T;
+        const bool interior = (t0 > 0) && (t0 + L + 6 <= T);
+        const bool edge_path = __any_sync(0xffffffffu, active && !interior);
+        const int ch = static_cast<int>(cch) * p.CC + 2 * pair;
+        const SnakeCoef coef = make_coef<PRECISE>(alpha[ch], alpha[ch + 1], beta[ch], beta[ch + 1]);
+        TOut* yrel = y + (static_cast<int64_t>(b) * T + t0) * C + ch;
+
+        ActEdge e;
+        e.rel_lo = e.rel_hi = 0;
+        e.m_valid = static_cast<int>(min(static_cast<int64_t>(L + 64), T - (t0 - 3)));
+        e.n_out = static_cast<int>(min(static_cast<int64_t>(L), T - t0));
+        e.first_seg = (t0 == 0);
+
+        float2 xw[7], ve[7], vo[7], cur[7];
+        float2 vlast = splat(0.f), xlast = splat(0.f);
+        // slab 0: rows t0-7 .. t0-1; the window starts with rows t0-6 .. t0-1
+        mbar_wait(&full[st], ph);
+        {
+            const uint8_t* sp = smem + st * p.stage_bytes + my_off;
+#pragma unroll
+            for (int j = 0; j < 6; ++j) xw[j] = SmemPair<TIn>::load(sp + (j + 1) * p.row_bytes);
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty[st]);
+        if (++st == p.stages) { st = 0; ph ^= 1; }
+#pragma unroll
+        for (int s = 0; s < 7; ++s) ve[s] = vo[s] = splat(0.f);
+
+#pragma unroll 1
+        for (int body = 0; body < p.nbody; ++body) {
+            mbar_wait(&full[st], ph);
+            {
+                const uint8_t* sp = smem + st * p.stage_bytes + my_off;
+#pragma unroll
+                for (int s = 0; s < 7; ++s) cur[s] = SmemPair<TIn>::load(sp + s * p.row_bytes);
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&empty[st]);
+            if (++st == p.stages) { st = 0; ph ^= 1; }
+            if (!active) continue;
+            const int g0 = 7 * body;
+            if (edge_path) {
+                // replicate padding of x: rows >= T repeat x[T-1]; rows < 0 (first segment only) repeat x[0]
+#pragma unroll
+                for (int s = 0; s < 7; ++s) {
+                    if (t0 + g0 + s >= T) cur[s] = xlast; else xlast = cur[s];
+                }
+                if (body == 0) {
+                    if (e.first_seg) {
+#pragma unroll
+                        for (int j = 0; j < 6; ++j) xw[j] = cur[0];
+                    }
+                    act1d_nlc_body<TOut, PRECISE, true, true>(xw, ve, vo, cur, vlast, coef, e, 0, yrel, C);
+                } else {
+                    act1d_nlc_body<TOut, PRECISE, true, false>(xw, ve, vo, cur, vlast, coef, e, g0, yrel, C);
+                }
+            } else {
+                if (body == 0)
+                    act1d_nlc_body<TOut, PRECISE, false, true>(xw, ve, vo, cur, vlast, coef, e, 0, yrel, C);
+                else
+                    act1d_nlc_body<TOut, PRECISE, false, false>(xw, ve, vo, cur, vlast, coef, e, g0, yrel, C);
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------------
 // [B,C,T] kernel with a TMA-staged halo'd time tile
 // ------------------------------------------------------------------------------------------------------------
 constexpr int NCL_THREADS = 128;
@@ -422,6 +591,85 @@ static int launch_nlc(const void* x, void* y, const float* alpha, const float* b
     return BVG_OK;
 }
 
+// TMA-pipelined launcher.  Returns BVG_OK after launching, or a positive value when the shape does not suit the TMA
+// path (C not a multiple of 8, ...) and the caller should use the direct-load kernel.
+template <typename TIn, typename TOut>
+static int launch_nlc_tma(const void* x, void* y, const float* alpha, const float* beta, int64_t B, int64_t T, int64_t C,
+                          int precise, cudaStream_t st) {
+    if (C % 8 != 0 || T >= (int64_t(1) << 31) - 4096 || reinterpret_cast<uintptr_t>(x) % 16 != 0) return 1;
+    ActTmaParams p{};
+    p.T = T;
+    p.C = static_cast<int>(C);
+    int CC = 0;
+    for (int c = 64; c >= 8; c -= 8)
+        if (C % c == 0) { CC = c; break; }
+    p.CC = CC;
+    p.P = CC / 2;
+    p.nsegs = ACT_TMA_COMPUTE / p.P;
+    p.n_cchunks = static_cast<int>(C / CC);
+    const int sms = device_sm_count();
+    const int64_t want_units = 2ll * 2 * sms;
+    static const int kL[] = {120, 92, 64, 50, 36, 22, 15, 8};
+    int L = 8;
+    for (int cand : kL) {
+        if (B * ceil_div(T, (int64_t)p.nsegs * cand) * p.n_cchunks >= want_units) { L = cand; break; }
+    }
+    p.L = L;
+    p.nbody = (L + 6) / 7;
+    const int64_t groups = ceil_div(T, (int64_t)p.nsegs * L);
+    const int64_t units = B * groups * p.n_cchunks;
+    if (units >= (int64_t(1) << 31) || groups >= (int64_t(1) << 31)) return 1;
+    p.groups_per_b = static_cast<uint32_t>(groups);
+    p.n_units = static_cast<uint32_t>(units);
+    p.row_bytes = static_cast<uint32_t>(CC * sizeof(TIn));
+    p.seg_stride = static_cast<uint32_t>(round_up(7ll * p.row_bytes, 128));
+    p.stage_bytes = p.nsegs * p.seg_stride;
+    p.tx_bytes = p.nsegs * 7u * p.row_bytes;
+    int stages = static_cast<int>((100 * 1024) / p.stage_bytes);
+    if (stages > ACT_TMA_MAX_STAGES) stages = ACT_TMA_MAX_STAGES;
+    if (stages < 2) return 1;
+    p.stages = stages;
+    const uint32_t smem_bytes = stages * p.stage_bytes + 2 * ACT_TMA_MAX_STAGES * 8 + 128;
+
+    EncodeTiledFn enc = get_encode_fn();
+    BVG_REQUIRE(enc != nullptr, BVG_ERR_CUDA, "cuTensorMapEncodeTiled not available from the driver");
+    CUtensorMap map;
+    const uint64_t es = sizeof(TIn);
+    cuuint64_t dims[3] = {(cuuint64_t)C, (cuuint64_t)T, (cuuint64_t)B};
+    cuuint64_t strides[2] = {(cuuint64_t)C * es, (cuuint64_t)C * (cuuint64_t)T * es};
+    cuuint32_t box[3] = {(cuuint32_t)CC, 7, 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = enc(&map, sizeof(TIn) == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3,
+                     const_cast<void*>(x), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    BVG_REQUIRE(r == CUDA_SUCCESS, BVG_ERR_CUDA, "cuTensorMapEncodeTiled(activation input) failed with CUresult %d", (int)r);
+
+    auto kern = precise ? act1d_nlc_tma_kernel<TIn, TOut, true> : act1d_nlc_tma_kernel<TIn, TOut, false>;
+    BVG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024));
+    const int grid = static_cast<int>(units < 2ll * sms ? units : 2ll * sms);
+    kern<<<grid, ACT_TMA_THREADS, smem_bytes, st>>>(map, static_cast<TOut*>(y), alpha, beta, p);
+    BVG_LAUNCH_CHECK("act1d_nlc_tma_kernel");
+    return BVG_OK;
+}
+
+static bool act_legacy_requested() {
+    static const bool v = []() {
+        const char* e = getenv("BVG_ACT_DIRECT");
+        return e != nullptr && e[0] == '1';
+    }();
+    return v;
+}
+
+template <typename TIn, typename TOut>
+static int launch_nlc_any(const void* x, void* y, const float* alpha, const float* beta, int64_t B, int64_t T, int64_t C,
+                          int precise, cudaStream_t st) {
+    if (!act_legacy_requested()) {
+        const int rc = launch_nlc_tma<TIn, TOut>(x, y, alpha, beta, B, T, C, precise, st);
+        if (rc <= 0) return rc;
+    }
+    return launch_nlc<TIn, TOut>(x, y, alpha, beta, B, T, C, precise, st);
+}
+
 int activation1d_nlc(const void* x, int x_dtype, void* y, int y_dtype, const float* alpha, const float* beta,
                      int64_t B, int64_t T, int64_t C, int precise, cudaStream_t st) {
     BVG_REQUIRE(x && y && alpha && beta, BVG_ERR_INVALID, "activation1d_nlc: null pointer");
@@ -431,12 +679,12 @@ int activation1d_nlc(const void* x, int x_dtype, void* y, int y_dtype, const flo
     BVG_REQUIRE(B <= 65535, BVG_ERR_UNSUPPORTED, "activation1d_nlc: B=%lld > 65535", (long long)B);
     if (B == 0 || T == 0) return BVG_OK;
     if (x_dtype == BVG_F32 && y_dtype == BVG_BF16)
-        return launch_nlc<float, __nv_bfloat16>(x, y, alpha, beta, B, T, C, precise, st);
-    if (x_dtype == BVG_F32 && y_dtype == BVG_F32) return launch_nlc<float, float>(x, y, alpha, beta, B, T, C, precise, st);
+        return launch_nlc_any<float, __nv_bfloat16>(x, y, alpha, beta, B, T, C, precise, st);
+    if (x_dtype == BVG_F32 && y_dtype == BVG_F32) return launch_nlc_any<float, float>(x, y, alpha, beta, B, T, C, precise, st);
     if (x_dtype == BVG_BF16 && y_dtype == BVG_BF16)
-        return launch_nlc<__nv_bfloat16, __nv_bfloat16>(x, y, alpha, beta, B, T, C, precise, st);
+        return launch_nlc_any<__nv_bfloat16, __nv_bfloat16>(x, y, alpha, beta, B, T, C, precise, st);
     if (x_dtype == BVG_BF16 && y_dtype == BVG_F32)
-        return launch_nlc<__nv_bfloat16, float>(x, y, alpha, beta, B, T, C, precise, st);
+        return launch_nlc_any<__nv_bfloat16, float>(x, y, alpha, beta, B, T, C, precise, st);
     return set_error(BVG_ERR_UNSUPPORTED, "activation1d_nlc: unsupported dtypes %d -> %d", x_dtype, y_dtype);
 }
 

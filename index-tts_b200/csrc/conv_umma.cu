@@ -24,6 +24,7 @@
 // so the epilogue of tile i overlaps the MMAs of tile i+1.
 #include "bvg_common.cuh"
 #include "sm100_ptx.cuh"
+#include "tma_host.cuh"
 
 namespace bvg {
 
@@ -69,6 +70,110 @@ struct ConvUmmaParams {
     int ld_stages;     // residual/accum chunk ring depth (<= UMMA_MAX_STAGES)
     float out_scale;
 };
+
+// Tile index -> (n tile, m tile, batch item), 32-bit arithmetic (total_tiles < 2^31 is checked by the launcher).
+struct TileCoord {
+    int nt, mt, b;
+};
+__device__ __forceinline__ TileCoord decode_tile(uint32_t tile, uint32_t n_tiles, uint32_t m_tiles) {
+    TileCoord c;
+    uint32_t rest = tile;
+    c.nt = 0;
+    if (n_tiles > 1) {
+        rest = tile / n_tiles;
+        c.nt = static_cast<int>(tile - rest * n_tiles);
+    }
+    const uint32_t b = rest / m_tiles;
+    c.mt = static_cast<int>(rest - b * m_tiles);
+    c.b = static_cast<int>(b);
+    return c;
+}
+
+// tcgen05.mma with the 64-bit shared-memory descriptors assembled from a 32-bit cursor (start-address field, i.e.
+// byte address >> 4) and the constant upper half: advancing an operand is one 32-bit uniform add.
+__device__ __forceinline__ void umma_f16_lo(uint32_t d_tmem, uint32_t a_lo, uint32_t b_lo, uint32_t desc_hi,
+                                            uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        ".reg .b64 da, db;\n"
+        "setp.ne.b32 p, %5, 0;\n"
+        "mov.b64 da, {%1, %3};\n"
+        "mov.b64 db, {%2, %3};\n"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %4, p;\n"
+        "}\n"
+        ::"r"(d_tmem), "r"(a_lo), "r"(b_lo), "r"(desc_hi), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+
+// The UMMA issue loop of warp 1.  For the small-channel layers one tap is only 16-48 tensor-pipe cycles per UMMA, so
+// this single-warp instruction stream IS the critical path (ncu r01c: 200 cycles per tap before this rewrite): it is
+// specialised on the weight mode, keeps every cursor in 32-bit (uniform) registers and touches no kernel parameter
+// inside the tap loop.
+template <bool STAT>
+__device__ __forceinline__ void umma_issue_loop(const ConvUmmaParams& p, uint32_t tmem_base, uint32_t sA_d, uint32_t sB_d,
+                                                uint64_t* a_full, uint64_t* a_empty, uint64_t* b_full, uint64_t* b_empty,
+                                                uint64_t* acc_full, uint64_t* acc_empty, int k_blocks, int n_tiles) {
+    const uint32_t idesc = umma_idesc_bf16_f32(UMMA_BLOCK_M, p.n_tile);
+    const uint32_t desc_hi = static_cast<uint32_t>(umma_desc_sw128_kmajor(0) >> 32);
+    const uint32_t tap_step = static_cast<uint32_t>(p.dil) * 8u;  // dil rows * 128 B >> 4
+    const uint32_t b_step = p.b_stage_bytes >> 4;
+    const uint32_t a_stage_d = p.a_stage_bytes >> 4;
+    const int taps = p.taps;
+    const int a_stages = p.a_stages, b_stages = p.b_stages;
+    const int last_steps = ((p.Cin - (k_blocks - 1) * UMMA_BLOCK_K) + 15) / 16;
+    const uint32_t n_tile = p.n_tile;
+    const uint32_t w_tile_d = static_cast<uint32_t>(k_blocks * taps) * b_step;  // stationary weights of one n tile
+    const uint32_t total = static_cast<uint32_t>(p.total_tiles);
+    const bool leader = elect_one();
+    int sa = 0, sb = 0;
+    uint32_t acc = 0, pa = 0, pb = 0, pacc = 0;
+    if (STAT) mbar_wait(&b_full[0], 0);
+    for (uint32_t tile = blockIdx.x; tile < total; tile += gridDim.x) {
+        mbar_wait(&acc_empty[acc], pacc ^ 1);
+        tc_fence_after_sync();
+        const uint32_t d_tmem = tmem_base + acc * n_tile;
+        uint32_t accumulate = 0;
+        uint32_t w_d = sB_d;  // stationary weight cursor
+        if (STAT && n_tiles > 1) w_d += (tile % static_cast<uint32_t>(n_tiles)) * w_tile_d;
+        for (int kb = 0; kb < k_blocks; ++kb) {
+            const int k_steps = (kb + 1 == k_blocks) ? last_steps : 4;
+            const bool k2 = k_steps > 1, k3 = k_steps > 2, k4 = k_steps > 3;
+            mbar_wait(&a_full[sa], pa);
+            tc_fence_after_sync();
+            uint32_t a_d = sA_d + sa * a_stage_d;
+#pragma unroll 1
+            for (int j = 0; j < taps; ++j) {
+                uint32_t b_d;
+                if (STAT) {
+                    b_d = w_d;
+                    w_d += b_step;
+                } else {
+                    mbar_wait(&b_full[sb], pb);
+                    tc_fence_after_sync();
+                    b_d = sB_d + sb * b_step;
+                }
+                if (leader) {
+                    umma_f16_lo(d_tmem, a_d, b_d, desc_hi, idesc, accumulate);
+                    if (k2) umma_f16_lo(d_tmem, a_d + 2, b_d + 2, desc_hi, idesc, 1);
+                    if (k3) umma_f16_lo(d_tmem, a_d + 4, b_d + 4, desc_hi, idesc, 1);
+                    if (k4) umma_f16_lo(d_tmem, a_d + 6, b_d + 6, desc_hi, idesc, 1);
+                    if (!STAT) umma_commit(&b_empty[sb]);
+                }
+                accumulate = 1;
+                a_d += tap_step;
+                if (!STAT) {
+                    if (++sb == b_stages) { sb = 0; pb ^= 1; }
+                }
+            }
+            if (leader) umma_commit(&a_empty[sa]);
+            if (++sa == a_stages) { sa = 0; pa ^= 1; }
+        }
+        if (leader) umma_commit(&acc_full[acc]);
+        acc ^= 1;
+        if (acc == 0) pacc ^= 1;
+    }
+}
 
 __global__ void __launch_bounds__(UMMA_THREADS, 1)
 conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_w,
@@ -118,6 +223,8 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
 
     const int k_blocks = (p.Cin + UMMA_BLOCK_K - 1) / UMMA_BLOCK_K;
     const int n_tiles = p.num_phases * p.tiles_per_phase;
+    const uint32_t total_tiles = static_cast<uint32_t>(p.total_tiles);
+    const uint32_t m_tiles = static_cast<uint32_t>(p.m_tiles);
 
     if (warp == 0) {
         // ------------------------------ TMA producer ------------------------------
@@ -137,14 +244,12 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
         }
         int sa = 0, sb = 0;
         uint32_t pa = 0, pb = 0;
-        for (int64_t tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
-            const int nt = static_cast<int>(tile % n_tiles);
-            const int64_t rest = tile / n_tiles;
-            const int64_t mt = rest % p.m_tiles;
-            const int b = static_cast<int>(rest / p.m_tiles);
+        for (uint32_t tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+            const TileCoord tc = decode_tile(tile, n_tiles, m_tiles);
+            const int nt = tc.nt, mt = tc.mt, b = tc.b;
             const int phase = nt / p.tiles_per_phase;
             const int n0 = phase * p.cout_phase + (nt % p.tiles_per_phase) * p.n_tile;
-            const int row0 = static_cast<int>(mt * UMMA_BLOCK_M) + p.tap_base[phase];
+            const int row0 = mt * UMMA_BLOCK_M + p.tap_base[phase];
             for (int kb = 0; kb < k_blocks; ++kb) {
                 mbar_wait(&a_empty[sa], pa ^ 1);
                 if (elect_one()) {
@@ -167,74 +272,21 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
         }
     } else if (warp == 1) {
         // ------------------------------ UMMA issuer ------------------------------
-        {
-            // Single-thread issue loop: everything loop-invariant is hoisted and the shared-memory descriptors are
-            // advanced by integer adds (start-address field = byte address >> 4), so one UMMA costs a few instructions.
-            const uint32_t idesc = umma_idesc_bf16_f32(UMMA_BLOCK_M, p.n_tile);
-            const uint64_t desc_hi = umma_desc_sw128_kmajor(0);           // layout/SBO/version bits, address 0
-            const uint32_t tap_step = static_cast<uint32_t>(p.dil) * 8u;  // dil rows * 128 B >> 4
-            const uint32_t b_step = p.b_stage_bytes >> 4;
-            const int taps = p.taps;
-            const int a_stages = p.a_stages, b_stages = p.b_stages;
-            const bool stationary = p.stationary != 0;
-            const int last_steps = ((p.Cin - (k_blocks - 1) * UMMA_BLOCK_K) + 15) / 16;
-            const uint32_t sA_d = smem_u32(sA) >> 4, sB_d = smem_u32(sB) >> 4;
-            const uint32_t a_stage_d = p.a_stage_bytes >> 4;
-            int sa = 0, sb = 0, acc = 0;
-            uint32_t pa = 0, pb = 0, pacc = 0;
-            if (stationary) mbar_wait(&b_full[0], 0);
-            for (int64_t tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
-                const int nt = static_cast<int>(tile % n_tiles);
-                mbar_wait(&acc_empty[acc], pacc ^ 1);
-                tc_fence_after_sync();
-                const uint32_t d_tmem = tmem_base + acc * p.n_tile;
-                uint32_t accumulate = 0;
-                uint32_t w_d = sB_d + static_cast<uint32_t>(nt * k_blocks * taps) * b_step;  // stationary weight cursor
-                for (int kb = 0; kb < k_blocks; ++kb) {
-                    const int k_steps = (kb + 1 == k_blocks) ? last_steps : 4;
-                    mbar_wait(&a_full[sa], pa);
-                    tc_fence_after_sync();
-                    uint64_t a_desc = desc_hi | static_cast<uint64_t>(sA_d + sa * a_stage_d);
-                    for (int j = 0; j < taps; ++j) {
-                        uint64_t b_desc;
-                        if (stationary) {
-                            b_desc = desc_hi | static_cast<uint64_t>(w_d);
-                            w_d += b_step;
-                        } else {
-                            mbar_wait(&b_full[sb], pb);
-                            tc_fence_after_sync();
-                            b_desc = desc_hi | static_cast<uint64_t>(sB_d + sb * b_step);
-                        }
-                        if (elect_one()) {
-                            umma_f16(d_tmem, a_desc, b_desc, idesc, accumulate);
-                            if (k_steps > 1) umma_f16(d_tmem, a_desc + 2, b_desc + 2, idesc, 1);
-                            if (k_steps > 2) umma_f16(d_tmem, a_desc + 4, b_desc + 4, idesc, 1);
-                            if (k_steps > 3) umma_f16(d_tmem, a_desc + 6, b_desc + 6, idesc, 1);
-                            if (!stationary) umma_commit(&b_empty[sb]);
-                        }
-                        accumulate = 1;
-                        a_desc += tap_step;
-                        if (!stationary) {
-                            if (++sb == b_stages) { sb = 0; pb ^= 1; }
-                        }
-                    }
-                    if (elect_one()) umma_commit(&a_empty[sa]);
-                    if (++sa == a_stages) { sa = 0; pa ^= 1; }
-                }
-                if (elect_one()) umma_commit(&acc_full[acc]);
-                if (++acc == 2) { acc = 0; pacc ^= 1; }
-            }
-        }
+        const uint32_t sA_d = smem_u32(sA) >> 4, sB_d = smem_u32(sB) >> 4;
+        if (p.stationary)
+            umma_issue_loop<true>(p, tmem_base, sA_d, sB_d, a_full, a_empty, b_full, b_empty, acc_full, acc_empty, k_blocks,
+                                  n_tiles);
+        else
+            umma_issue_loop<false>(p, tmem_base, sA_d, sB_d, a_full, a_empty, b_full, b_empty, acc_full, acc_empty,
+                                   k_blocks, n_tiles);
     } else if (warp == 6) {
         // ------------------------------ residual / accum chunk loader ------------------------------
         if (n_ld > 0) {
             int s = 0;
             uint32_t ps = 0;
-            for (int64_t tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
-                const int nt = static_cast<int>(tile % n_tiles);
-                const int64_t rest = tile / n_tiles;
-                const int t0 = static_cast<int>((rest % p.m_tiles) * UMMA_BLOCK_M);
-                const int b = static_cast<int>(rest / p.m_tiles);
+            for (uint32_t tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+                const TileCoord tc = decode_tile(tile, n_tiles, m_tiles);
+                const int nt = tc.nt, t0 = tc.mt * UMMA_BLOCK_M, b = tc.b;
                 const int phase = nt / p.tiles_per_phase;
                 const int c0 = (nt % p.tiles_per_phase) * p.n_tile;
                 for (int c = 0; c < p.n_tile; c += EPI_CHUNK) {
@@ -262,11 +314,9 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
         uint8_t* st16 = sSt16 + q * 2 * EPI_ST16_TILE_BYTES;
         int acc = 0, ls = 0, ob = 0;
         uint32_t pacc = 0, pls = 0;
-        for (int64_t tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
-            const int nt = static_cast<int>(tile % n_tiles);
-            const int64_t rest = tile / n_tiles;
-            const int t0 = static_cast<int>((rest % p.m_tiles) * UMMA_BLOCK_M);
-            const int b = static_cast<int>(rest / p.m_tiles);
+        for (uint32_t tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+            const TileCoord tc = decode_tile(tile, n_tiles, m_tiles);
+            const int nt = tc.nt, t0 = tc.mt * UMMA_BLOCK_M, b = tc.b;
             const int phase = nt / p.tiles_per_phase;
             const int c0 = (nt % p.tiles_per_phase) * p.n_tile;  // channel offset inside the phase
 
@@ -381,31 +431,6 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
 // ------------------------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------------------------
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
-                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
-                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-static EncodeTiledFn get_encode_fn() {
-    static EncodeTiledFn fn = []() -> EncodeTiledFn {
-        void* f = nullptr;
-        cudaDriverEntryPointQueryResult q;
-        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) != cudaSuccess) return nullptr;
-        return reinterpret_cast<EncodeTiledFn>(f);
-    }();
-    return fn;
-}
-
-static int device_sm_count() {
-    static thread_local int cached_dev = -1, cached = 0;
-    int dev = 0;
-    cudaGetDevice(&dev);
-    if (dev != cached_dev) {
-        cudaDeviceGetAttribute(&cached, cudaDevAttrMultiProcessorCount, dev);
-        cached_dev = dev;
-    }
-    return cached;
-}
-
 static int encode_3d_bf16(CUtensorMap* map, const void* ptr, uint64_t d0, uint64_t d1, uint64_t d2, uint32_t b0,
                           uint32_t b1, uint32_t b2, const char* what) {
     EncodeTiledFn enc = get_encode_fn();
@@ -474,6 +499,8 @@ int conv_umma_launch(const void* x, const void* w_packed, const float* bias, con
     }
     p.m_tiles = ceil_div(T, UMMA_BLOCK_M);
     p.total_tiles = p.m_tiles * B * p.num_phases * p.tiles_per_phase;
+    BVG_REQUIRE(p.total_tiles < (int64_t(1) << 31) - 1024, BVG_ERR_UNSUPPORTED, "conv_umma: %lld tiles exceed the 32-bit tile index",
+                (long long)p.total_tiles);
     const int a_rows = (int)round_up(UMMA_BLOCK_M + (taps - 1) * dil, 8);
     p.a_stage_bytes = (uint32_t)round_up((int64_t)a_rows * 128, 1024);
     p.b_stage_bytes = (uint32_t)round_up((int64_t)p.n_tile * 128, 1024);
