@@ -23,6 +23,10 @@
 
 #include <cstdlib>
 
+#ifndef BVG_ACT_SMEM_KB_DEFAULT
+#define BVG_ACT_SMEM_KB_DEFAULT 100
+#endif
+
 namespace bvg {
 
 __device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) { return __ffma2_rn(a, b, c); }
@@ -625,7 +629,12 @@ static int launch_nlc_tma(const void* x, void* y, const float* alpha, const floa
     p.seg_stride = static_cast<uint32_t>(round_up(7ll * p.row_bytes, 128));
     p.stage_bytes = p.nsegs * p.seg_stride;
     p.tx_bytes = p.nsegs * 7u * p.row_bytes;
-    int stages = static_cast<int>((100 * 1024) / p.stage_bytes);
+    static const int ring_kb = []() {
+        const char* e = getenv("BVG_ACT_SMEM_KB");
+        const int kb = e ? atoi(e) : 0;
+        return (kb >= 16 && kb <= 100) ? kb : BVG_ACT_SMEM_KB_DEFAULT;
+    }();
+    int stages = static_cast<int>((ring_kb * 1024) / p.stage_bytes);
     if (stages > ACT_TMA_MAX_STAGES) stages = ACT_TMA_MAX_STAGES;
     if (stages < 2) return 1;
     p.stages = stages;
@@ -646,7 +655,12 @@ static int launch_nlc_tma(const void* x, void* y, const float* alpha, const floa
 
     auto kern = precise ? act1d_nlc_tma_kernel<TIn, TOut, true> : act1d_nlc_tma_kernel<TIn, TOut, false>;
     BVG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024));
-    const int grid = static_cast<int>(units < 2ll * sms ? units : 2ll * sms);
+    // same L1/shared split as the conv kernel: CTAs of the two kernels can then be resident on one SM at the same time
+    BVG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    static const int grid_mode = []() { const char* e = getenv("BVG_ACT_GRID"); return e ? atoi(e) : 0; }();
+    int grid = static_cast<int>(units < 2ll * sms ? units : 2ll * sms);
+    if (grid_mode == 1) grid = static_cast<int>(units);                      // one unit per CTA: hardware load balancing
+    if (grid_mode == 2) grid = static_cast<int>(units < sms ? units : sms);  // one CTA per SM
     kern<<<grid, ACT_TMA_THREADS, smem_bytes, st>>>(map, static_cast<TOut*>(y), alpha, beta, p);
     BVG_LAUNCH_CHECK("act1d_nlc_tma_kernel");
     return BVG_OK;

@@ -26,11 +26,18 @@
 #include "sm100_ptx.cuh"
 #include "tma_host.cuh"
 
+#include <cstdlib>
+
+#ifndef BVG_CONV_SMEM_KB_DEFAULT
+#define BVG_CONV_SMEM_KB_DEFAULT 227
+#endif
+
 namespace bvg {
 
 constexpr int UMMA_BLOCK_M = 128;
 constexpr int UMMA_BLOCK_K = 64;  // bf16 elements per 128-byte swizzled row
-constexpr int UMMA_THREADS = 224;  // 7 warps: TMA producer, UMMA issuer, 4 epilogue, residual loader
+constexpr int UMMA_THREADS = 224;   // 7 warps: TMA producer, UMMA issuer, 4 epilogue, residual loader
+constexpr int UMMA_THREADS2 = 384;  // dual pipeline: + a second UMMA issuer (warp 7) and 4 more epilogue warps (8..11)
 constexpr int UMMA_MAX_STAGES = 8;
 constexpr int EPI_CHUNK = 32;                  // accumulator columns per epilogue step (= one 128-byte fp32 row segment)
 constexpr int EPI_LD_TILE_BYTES = 128 * 128;   // one residual / accum chunk: 128 rows x 32 fp32, 128B-swizzled
@@ -59,6 +66,10 @@ struct ConvUmmaParams {
     int a_stages, b_stages;
     uint32_t a_stage_bytes, b_stage_bytes;
     uint32_t tmem_cols;
+    // pipeline groups (1 or 2): group g owns the CTA's tiles i with i % ng == g, its own UMMA issuer warp, 4 epilogue
+    // warps, 2 TMEM accumulators and output staging tiles; the TMA producer / loader warps feed both in tile order.
+    // For small-channel layers a tile is ~1 us of single-warp instruction issue in each role, so two groups double it.
+    int ng;
     // weight-stationary mode: every (n tile, K block, tap) weight tile is loaded into shared memory ONCE per CTA and
     // only the activation halo tiles stream (small-channel layers, where re-streaming weights per 128-row tile made
     // the kernel TMA-latency bound)
@@ -113,26 +124,35 @@ __device__ __forceinline__ void umma_f16_lo(uint32_t d_tmem, uint32_t a_lo, uint
 template <bool STAT>
 __device__ __forceinline__ void umma_issue_loop(const ConvUmmaParams& p, uint32_t tmem_base, uint32_t sA_d, uint32_t sB_d,
                                                 uint64_t* a_full, uint64_t* a_empty, uint64_t* b_full, uint64_t* b_empty,
-                                                uint64_t* acc_full, uint64_t* acc_empty, int k_blocks, int n_tiles) {
+                                                uint64_t* acc_full, uint64_t* acc_empty, int k_blocks, int n_tiles,
+                                                int group) {
     const uint32_t idesc = umma_idesc_bf16_f32(UMMA_BLOCK_M, p.n_tile);
     const uint32_t desc_hi = static_cast<uint32_t>(umma_desc_sw128_kmajor(0) >> 32);
     const uint32_t tap_step = static_cast<uint32_t>(p.dil) * 8u;  // dil rows * 128 B >> 4
     const uint32_t b_step = p.b_stage_bytes >> 4;
     const uint32_t a_stage_d = p.a_stage_bytes >> 4;
     const int taps = p.taps;
-    const int a_stages = p.a_stages, b_stages = p.b_stages;
+    const int a_stages = p.a_stages / p.ng, b_stages = p.b_stages;  // A stages per pipeline group
     const int last_steps = ((p.Cin - (k_blocks - 1) * UMMA_BLOCK_K) + 15) / 16;
     const uint32_t n_tile = p.n_tile;
     const uint32_t w_tile_d = static_cast<uint32_t>(k_blocks * taps) * b_step;  // stationary weights of one n tile
     const uint32_t total = static_cast<uint32_t>(p.total_tiles);
     const bool leader = elect_one();
+    // each group consumes its own sub-ring of A stages (slots [group*a_stages, (group+1)*a_stages)), so a slot is
+    // always refilled for the same consumer and the parity protocol stays unambiguous
+    const int ng = p.ng;
+    acc_full += 2 * group;
+    acc_empty += 2 * group;
+    a_full += group * a_stages;
+    a_empty += group * a_stages;
+    sA_d += static_cast<uint32_t>(group * a_stages) * a_stage_d;
     int sa = 0, sb = 0;
     uint32_t acc = 0, pa = 0, pb = 0, pacc = 0;
     if (STAT) mbar_wait(&b_full[0], 0);
-    for (uint32_t tile = blockIdx.x; tile < total; tile += gridDim.x) {
+    for (uint32_t tile = blockIdx.x + group * gridDim.x; tile < total; tile += ng * gridDim.x) {
         mbar_wait(&acc_empty[acc], pacc ^ 1);
         tc_fence_after_sync();
-        const uint32_t d_tmem = tmem_base + acc * n_tile;
+        const uint32_t d_tmem = tmem_base + (2 * group + acc) * n_tile;
         uint32_t accumulate = 0;
         uint32_t w_d = sB_d;  // stationary weight cursor
         if (STAT && n_tiles > 1) w_d += (tile % static_cast<uint32_t>(n_tiles)) * w_tile_d;
@@ -175,7 +195,7 @@ __device__ __forceinline__ void umma_issue_loop(const ConvUmmaParams& p, uint32_
     }
 }
 
-__global__ void __launch_bounds__(UMMA_THREADS, 1)
+__global__ void __launch_bounds__(UMMA_THREADS2, 1)
 conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_w,
                  const __grid_constant__ CUtensorMap map_res, const __grid_constant__ CUtensorMap map_acc,
                  const __grid_constant__ CUtensorMap map_y32, const __grid_constant__ CUtensorMap map_y16,
@@ -189,15 +209,15 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
     uint8_t* sLd = sB + (p.stationary ? p.w_bytes : p.b_stages * p.b_stage_bytes);
     const int n_ld = p.has_res + p.has_acc;
     uint8_t* sSt32 = sLd + p.ld_stages * n_ld * EPI_LD_TILE_BYTES;
-    uint8_t* sSt16 = sSt32 + (p.has_y32 ? 4 * 2 * EPI_ST32_TILE_BYTES : 0);
-    uint64_t* bars = reinterpret_cast<uint64_t*>(sSt16 + (p.has_y16 ? 4 * 2 * EPI_ST16_TILE_BYTES : 0));
+    uint8_t* sSt16 = sSt32 + (p.has_y32 ? p.ng * 4 * 2 * EPI_ST32_TILE_BYTES : 0);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sSt16 + (p.has_y16 ? p.ng * 4 * 2 * EPI_ST16_TILE_BYTES : 0));
     uint64_t* a_full = bars;
     uint64_t* a_empty = bars + UMMA_MAX_STAGES;
     uint64_t* b_full = bars + 2 * UMMA_MAX_STAGES;   // [0] doubles as "weights resident" in stationary mode
     uint64_t* b_empty = bars + 3 * UMMA_MAX_STAGES;
-    uint64_t* acc_full = bars + 4 * UMMA_MAX_STAGES;  // [2]
-    uint64_t* acc_empty = acc_full + 2;               // [2]
-    uint64_t* ld_full = acc_empty + 2;                // [UMMA_MAX_STAGES]
+    uint64_t* acc_full = bars + 4 * UMMA_MAX_STAGES;  // [2 per group]
+    uint64_t* acc_empty = acc_full + 4;               // [2 per group]
+    uint64_t* ld_full = acc_empty + 4;                // [UMMA_MAX_STAGES]
     uint64_t* ld_empty = ld_full + UMMA_MAX_STAGES;   // [UMMA_MAX_STAGES]
     uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(ld_empty + UMMA_MAX_STAGES);
 
@@ -212,7 +232,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
             mbar_init(&b_full[i], 1); mbar_init(&b_empty[i], 1);
             mbar_init(&ld_full[i], 1); mbar_init(&ld_empty[i], 4);
         }
-        for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 4); }
+        for (int i = 0; i < 4; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 4); }
         fence_barrier_init();
     }
     if (warp == 1) tmem_alloc(tmem_ptr, p.tmem_cols);
@@ -242,21 +262,24 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                                              kb * UMMA_BLOCK_K, n0, j, kPolicyEvictLast);
             }
         }
-        int sa = 0, sb = 0;
-        uint32_t pa = 0, pb = 0;
+        // per-group cursors into the groups' A sub-rings (tiles alternate between the groups)
+        const int a_per = p.a_stages / p.ng;
+        int sa = 0, sa_other = 0, sb = 0, g = 0;
+        uint32_t pa = 0, pa_other = 0, pb = 0;
         for (uint32_t tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
             const TileCoord tc = decode_tile(tile, n_tiles, m_tiles);
             const int nt = tc.nt, mt = tc.mt, b = tc.b;
+            const int slot0 = g * a_per;
             const int phase = nt / p.tiles_per_phase;
             const int n0 = phase * p.cout_phase + (nt % p.tiles_per_phase) * p.n_tile;
             const int row0 = mt * UMMA_BLOCK_M + p.tap_base[phase];
             for (int kb = 0; kb < k_blocks; ++kb) {
-                mbar_wait(&a_empty[sa], pa ^ 1);
+                mbar_wait(&a_empty[slot0 + sa], pa ^ 1);
                 if (elect_one()) {
-                    mbar_arrive_expect_tx(&a_full[sa], p.a_stage_bytes);
-                    tma_load_3d(sA + sa * p.a_stage_bytes, &map_x, &a_full[sa], kb * UMMA_BLOCK_K, row0, b);
+                    mbar_arrive_expect_tx(&a_full[slot0 + sa], p.a_stage_bytes);
+                    tma_load_3d(sA + (slot0 + sa) * p.a_stage_bytes, &map_x, &a_full[slot0 + sa], kb * UMMA_BLOCK_K, row0, b);
                 }
-                if (++sa == p.a_stages) { sa = 0; pa ^= 1; }
+                if (++sa == a_per) { sa = 0; pa ^= 1; }
                 if (!p.stationary) {
                     for (int j = 0; j < p.taps; ++j) {
                         mbar_wait(&b_empty[sb], pb ^ 1);
@@ -269,52 +292,75 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                     }
                 }
             }
+            if (p.ng == 2) {  // next tile belongs to the other group
+                int ts = sa; sa = sa_other; sa_other = ts;
+                uint32_t tp = pa; pa = pa_other; pa_other = tp;
+                g ^= 1;
+            }
         }
-    } else if (warp == 1) {
-        // ------------------------------ UMMA issuer ------------------------------
+    } else if (warp == 1 || warp == 7) {
+        // ------------------------------ UMMA issuer (one per pipeline group) ------------------------------
+        const int group = warp == 7 ? 1 : 0;
         const uint32_t sA_d = smem_u32(sA) >> 4, sB_d = smem_u32(sB) >> 4;
         if (p.stationary)
             umma_issue_loop<true>(p, tmem_base, sA_d, sB_d, a_full, a_empty, b_full, b_empty, acc_full, acc_empty, k_blocks,
-                                  n_tiles);
+                                  n_tiles, group);
         else
             umma_issue_loop<false>(p, tmem_base, sA_d, sB_d, a_full, a_empty, b_full, b_empty, acc_full, acc_empty,
-                                   k_blocks, n_tiles);
+                                   k_blocks, n_tiles, group);
     } else if (warp == 6) {
         // ------------------------------ residual / accum chunk loader ------------------------------
         if (n_ld > 0) {
-            int s = 0;
-            uint32_t ps = 0;
+            // like the A ring, the chunk ring is split into one sub-ring per pipeline group: a slot is then always
+            // refilled for the same consumer warps, which keeps the parity protocol unambiguous
+            const int ld_per = p.ld_stages / p.ng;
+            int s = 0, s_other = 0, g = 0;
+            uint32_t ps = 0, ps_other = 0;
             for (uint32_t tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
                 const TileCoord tc = decode_tile(tile, n_tiles, m_tiles);
                 const int nt = tc.nt, t0 = tc.mt * UMMA_BLOCK_M, b = tc.b;
                 const int phase = nt / p.tiles_per_phase;
                 const int c0 = (nt % p.tiles_per_phase) * p.n_tile;
+                const int slot0 = g * ld_per;
                 for (int c = 0; c < p.n_tile; c += EPI_CHUNK) {
-                    mbar_wait(&ld_empty[s], ps ^ 1);
+                    const int slot = slot0 + s;
+                    mbar_wait(&ld_empty[slot], ps ^ 1);
                     if (elect_one()) {
-                        mbar_arrive_expect_tx(&ld_full[s], n_ld * EPI_LD_TILE_BYTES);
-                        uint8_t* dst = sLd + s * n_ld * EPI_LD_TILE_BYTES;
-                        if (p.has_res) tma_load_4d(dst, &map_res, &ld_full[s], c0 + c, phase, t0, b);
+                        mbar_arrive_expect_tx(&ld_full[slot], n_ld * EPI_LD_TILE_BYTES);
+                        uint8_t* dst = sLd + slot * n_ld * EPI_LD_TILE_BYTES;
+                        if (p.has_res) tma_load_4d(dst, &map_res, &ld_full[slot], c0 + c, phase, t0, b);
                         if (p.has_acc)
-                            tma_load_4d(dst + p.has_res * EPI_LD_TILE_BYTES, &map_acc, &ld_full[s], c0 + c, phase, t0, b);
+                            tma_load_4d(dst + p.has_res * EPI_LD_TILE_BYTES, &map_acc, &ld_full[slot], c0 + c, phase, t0, b);
                     }
-                    if (++s == p.ld_stages) { s = 0; ps ^= 1; }
+                    if (++s == ld_per) { s = 0; ps ^= 1; }
+                }
+                if (p.ng == 2) {  // next tile belongs to the other group
+                    int ts = s; s = s_other; s_other = ts;
+                    uint32_t tp = ps; ps = ps_other; ps_other = tp;
+                    g ^= 1;
                 }
             }
         }
     } else {
-        // ------------------------------ epilogue (warps 2..5) ------------------------------
+        // ------------------------------ epilogue (warps 2..5; group 1: warps 8..11) ------------------------------
         // thread = accumulator row.  tcgen05.ld -> +bias (+residual chunk from smem) * scale (+accum chunk) -> swizzled
         // per-warp smem tiles -> TMA bulk tensor stores.  No direct global loads/stores except the bias broadcast.
         const int q = warp & 3;                 // TMEM lane quarter this warp may access
         const int row = q * 32 + lane;          // row inside the 128-row tile
         const uint32_t sw128 = static_cast<uint32_t>(row & 7);
         const uint32_t sw64 = static_cast<uint32_t>((lane >> 1) & 3);
-        uint8_t* st32 = sSt32 + q * 2 * EPI_ST32_TILE_BYTES;
-        uint8_t* st16 = sSt16 + q * 2 * EPI_ST16_TILE_BYTES;
+        const int group = warp >= 8 ? 1 : 0;
+        uint8_t* st32 = sSt32 + (group * 4 + q) * 2 * EPI_ST32_TILE_BYTES;
+        uint8_t* st16 = sSt16 + (group * 4 + q) * 2 * EPI_ST16_TILE_BYTES;
+        acc_full += 2 * group;
+        acc_empty += 2 * group;
+        const int ld_per = p.ld_stages / p.ng;  // this group's sub-ring of residual / accum chunk slots
+        const uint8_t* sLdG = sLd + group * ld_per * n_ld * EPI_LD_TILE_BYTES;
+        ld_full += group * ld_per;
+        ld_empty += group * ld_per;
         int acc = 0, ls = 0, ob = 0;
         uint32_t pacc = 0, pls = 0;
-        for (uint32_t tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        for (uint32_t tile = blockIdx.x + group * gridDim.x; tile < total_tiles; tile += p.ng * gridDim.x) {
             const TileCoord tc = decode_tile(tile, n_tiles, m_tiles);
             const int nt = tc.nt, t0 = tc.mt * UMMA_BLOCK_M, b = tc.b;
             const int phase = nt / p.tiles_per_phase;
@@ -322,7 +368,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
 
             mbar_wait(&acc_full[acc], pacc);
             tc_fence_after_sync();
-            const uint32_t t_addr = tmem_base + ((static_cast<uint32_t>(q) * 32u) << 16) + acc * p.n_tile;
+            const uint32_t t_addr = tmem_base + ((static_cast<uint32_t>(q) * 32u) << 16) + (2 * group + acc) * p.n_tile;
             for (int c = 0; c < p.n_tile; c += EPI_CHUNK) {
                 const int width = min(EPI_CHUNK, p.n_tile - c);  // 32 or 16
                 float o[32];
@@ -357,7 +403,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                 }
                 if (n_ld > 0) {
                     mbar_wait(&ld_full[ls], pls);
-                    const uint8_t* ld = sLd + ls * n_ld * EPI_LD_TILE_BYTES + row * 128;
+                    const uint8_t* ld = sLdG + ls * n_ld * EPI_LD_TILE_BYTES + row * 128;
                     if (p.has_res) {
 #pragma unroll
                         for (int j = 0; j < 8; ++j) {
@@ -377,7 +423,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                     }
                     __syncwarp();
                     if (lane == 0) mbar_arrive(&ld_empty[ls]);
-                    if (++ls == p.ld_stages) { ls = 0; pls ^= 1; }
+                    if (++ls == ld_per) { ls = 0; pls ^= 1; }
                 } else {
 #pragma unroll
                     for (int e = 0; e < 32; ++e) o[e] *= p.out_scale;
@@ -467,6 +513,18 @@ static int encode_io_4d(CUtensorMap* map, const void* ptr, bool bf16, uint64_t c
     return BVG_OK;
 }
 
+// Shared-memory budget of one CTA.  Below the 227 KB maximum an Activation1d CTA of another AMP block can be resident
+// on the same SM (forward.cu runs the blocks on separate streams), trading pipeline depth for FP32/tensor overlap.
+static int64_t conv_smem_budget() {
+    static const int64_t v = []() -> int64_t {
+        const char* e = getenv("BVG_CONV_SMEM_KB");
+        int kb = e ? atoi(e) : 0;
+        if (kb < 96 || kb > 227) kb = BVG_CONV_SMEM_KB_DEFAULT;
+        return (int64_t)kb * 1024;
+    }();
+    return v;
+}
+
 // Generic launcher: plain conv (num_phases = 1) or polyphase transposed conv.
 int conv_umma_launch(const void* x, const void* w_packed, const float* bias, const float* residual, const float* accum,
                      float* y_f32, void* y_bf16, int64_t B, int64_t T, int64_t Cin, int64_t N, int64_t cout_phase,
@@ -504,9 +562,7 @@ int conv_umma_launch(const void* x, const void* w_packed, const float* bias, con
     const int a_rows = (int)round_up(UMMA_BLOCK_M + (taps - 1) * dil, 8);
     p.a_stage_bytes = (uint32_t)round_up((int64_t)a_rows * 128, 1024);
     p.b_stage_bytes = (uint32_t)round_up((int64_t)p.n_tile * 128, 1024);
-    uint32_t tm = 32;
-    while (tm < (uint32_t)(2 * p.n_tile)) tm <<= 1;
-    p.tmem_cols = tm;
+    p.ng = 1;
     p.has_res = residual != nullptr; p.has_acc = accum != nullptr;
     p.has_y32 = y_f32 != nullptr; p.has_y16 = y_bf16 != nullptr;
     const int n_ld = p.has_res + p.has_acc;
@@ -516,39 +572,60 @@ int conv_umma_launch(const void* x, const void* w_packed, const float* bias, con
     // shared memory plan: 227 KB - alignment slack - barriers - epilogue tiles is what the operand pipelines get
     const int k_blocks = (int)ceil_div(Cin, UMMA_BLOCK_K);
     const int64_t w_all = (int64_t)p.num_phases * p.tiles_per_phase * k_blocks * taps * p.b_stage_bytes;
-    const uint32_t st_bytes = (p.has_y32 ? 8 * EPI_ST32_TILE_BYTES : 0) + (p.has_y16 ? 8 * EPI_ST16_TILE_BYTES : 0);
-    const uint32_t fixed = 1024 + 1024 + st_bytes;
-    const int64_t avail = 227 * 1024 - (int64_t)fixed;
-    const int64_t ld_stage_bytes = (int64_t)n_ld * EPI_LD_TILE_BYTES;
+    // dual pipeline when the weights are small enough to be stationary and four accumulators fit TMEM
+    static const int ng_env = []() { const char* e = getenv("BVG_CONV_GROUPS"); return e ? atoi(e) : 0; }();
+    if (ng_env != 1 && 4 * p.n_tile <= 512 && w_all <= 96 * 1024) p.ng = 2;
     bool planned = false;
-    if (w_all <= 112 * 1024 && avail - w_all >= 2 * (int64_t)p.a_stage_bytes + ld_stage_bytes) {
-        // weight-stationary: all weight tiles resident; the rest is split between a deep activation ring and a deep
-        // residual/accum ring (both hide DRAM latency, a tile is only ~1 us of work here)
-        p.stationary = 1;
-        p.w_bytes = (uint32_t)w_all;
-        p.b_stages = 0;
-        const int64_t rem = avail - w_all;
-        for (int ld = n_ld ? UMMA_MAX_STAGES : 0;; --ld) {
-            int64_t as = (rem - ld * ld_stage_bytes) / p.a_stage_bytes;
-            if (as > UMMA_MAX_STAGES) as = UMMA_MAX_STAGES;
-            if (as >= 4 || (ld <= 1 && as >= 2)) { p.a_stages = (int)as; p.ld_stages = ld; planned = true; break; }
-            if (ld <= 1) break;
+    uint32_t st_bytes = 0;
+    for (int ng_try = p.ng; ng_try >= 1 && !planned; --ng_try) {
+        p.ng = ng_try;
+        st_bytes = p.ng * ((p.has_y32 ? 8 * EPI_ST32_TILE_BYTES : 0) + (p.has_y16 ? 8 * EPI_ST16_TILE_BYTES : 0));
+        const uint32_t fixed = 1024 + 1024 + st_bytes;
+        // best effort: plan inside the (possibly reduced) budget first, fall back to the full 227 KB when a layer needs it
+        const int64_t budgets[2] = {conv_smem_budget(), 227 * 1024};
+        for (int attempt = 0; attempt < 2 && !planned; ++attempt) {
+            const int64_t avail = budgets[attempt] - (int64_t)fixed;
+            const int64_t ld_stage_bytes = (int64_t)n_ld * EPI_LD_TILE_BYTES;
+            if (w_all <= 112 * 1024 && avail - w_all >= 2 * (int64_t)p.a_stage_bytes + ld_stage_bytes) {
+                // weight-stationary: all weight tiles resident; the rest is split between a deep activation ring and a deep
+                // residual/accum ring (both hide DRAM latency, a tile is only ~1 us of work here)
+                p.stationary = 1;
+                p.w_bytes = (uint32_t)w_all;
+                p.b_stages = 0;
+                const int64_t rem = avail - w_all;
+                // both rings are split evenly between the pipeline groups, so their depths are multiples of ng
+                const int ld_min = n_ld ? p.ng : 0;
+                for (int ld = n_ld ? UMMA_MAX_STAGES : 0;; ld -= p.ng) {
+                    int64_t as = (rem - ld * ld_stage_bytes) / p.a_stage_bytes;
+                    if (as > UMMA_MAX_STAGES) as = UMMA_MAX_STAGES;
+                    as -= as % p.ng;
+                    if (as >= 4 || (ld <= ld_min && as >= 2)) { p.a_stages = (int)as; p.ld_stages = ld; planned = true; break; }
+                    if (ld <= ld_min) break;
+                }
+            }
+            if (!planned) {
+                p.stationary = 0;
+                p.w_bytes = 0;
+                for (int ld = n_ld ? 4 : 0;; --ld) {
+                    const int64_t rem = avail - ld * ld_stage_bytes;
+                    int as = 3;
+                    int64_t bs = (rem - 3 * (int64_t)p.a_stage_bytes) / p.b_stage_bytes;
+                    if (bs < 4) { as = 2; bs = (rem - 2 * (int64_t)p.a_stage_bytes) / p.b_stage_bytes; }
+                    if (bs > UMMA_MAX_STAGES) bs = UMMA_MAX_STAGES;
+                    if (bs >= 4 || (ld <= 1 && bs >= 2)) { p.a_stages = as; p.b_stages = (int)bs; p.ld_stages = ld; planned = true; break; }
+                    if (ld <= 1) break;
+                }
+            }
         }
-    }
-    if (!planned) {
-        p.stationary = 0;
-        p.w_bytes = 0;
-        for (int ld = n_ld ? 4 : 0;; --ld) {
-            const int64_t rem = avail - ld * ld_stage_bytes;
-            int as = 3;
-            int64_t bs = (rem - 3 * (int64_t)p.a_stage_bytes) / p.b_stage_bytes;
-            if (bs < 4) { as = 2; bs = (rem - 2 * (int64_t)p.a_stage_bytes) / p.b_stage_bytes; }
-            if (bs > UMMA_MAX_STAGES) bs = UMMA_MAX_STAGES;
-            if (bs >= 4 || (ld <= 1 && bs >= 2)) { p.a_stages = as; p.b_stages = (int)bs; p.ld_stages = ld; planned = true; break; }
-            if (ld <= 1) break;
-        }
+        if (planned && p.ng == 2 && !p.stationary) planned = false;  // the dual pipeline needs resident weights
     }
     BVG_REQUIRE(planned, BVG_ERR_UNSUPPORTED, "conv_umma: tile does not fit shared memory");
+    BVG_REQUIRE(p.ng == 1 || p.stationary, BVG_ERR_UNSUPPORTED, "conv_umma: dual pipeline planned without stationary weights");
+    {
+        uint32_t tm = 32;
+        while (tm < (uint32_t)(2 * p.ng * p.n_tile)) tm <<= 1;
+        p.tmem_cols = tm;
+    }
     const uint32_t smem_bytes = p.a_stages * p.a_stage_bytes + (p.stationary ? p.w_bytes : p.b_stages * p.b_stage_bytes) +
                                 p.ld_stages * n_ld * EPI_LD_TILE_BYTES + st_bytes + 1024 + 1024;
     BVG_REQUIRE(smem_bytes <= 227 * 1024, BVG_ERR_UNSUPPORTED, "conv_umma: %u bytes of shared memory needed", smem_bytes);
@@ -569,6 +646,8 @@ int conv_umma_launch(const void* x, const void* w_packed, const float* bias, con
         BVG_CUDA(cudaGetDevice(&dev));
         if (dev < 0 || dev >= 64 || !attr_set[dev]) {
             BVG_CUDA(cudaFuncSetAttribute(conv_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+            BVG_CUDA(cudaFuncSetAttribute(conv_umma_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                          cudaSharedmemCarveoutMaxShared));
             if (dev >= 0 && dev < 64) attr_set[dev] = true;
         }
     }
@@ -579,7 +658,7 @@ int conv_umma_launch(const void* x, const void* w_packed, const float* bias, con
     if (p.has_acc && (rc = encode_io_4d(&map_acc, accum, false, cout_phase, num_phases, T, B, 128, "accum")) != BVG_OK) return rc;
     if (p.has_y32 && (rc = encode_io_4d(&map_y32, y_f32, false, cout_phase, num_phases, T, B, 32, "y_f32")) != BVG_OK) return rc;
     if (p.has_y16 && (rc = encode_io_4d(&map_y16, y_bf16, true, cout_phase, num_phases, T, B, 32, "y_bf16")) != BVG_OK) return rc;
-    conv_umma_kernel<<<grid, UMMA_THREADS, smem_bytes, st>>>(map_x, map_w, map_res, map_acc, map_y32, map_y16, p);
+    conv_umma_kernel<<<grid, p.ng == 2 ? UMMA_THREADS2 : UMMA_THREADS, smem_bytes, st>>>(map_x, map_w, map_res, map_acc, map_y32, map_y16, p);
     BVG_LAUNCH_CHECK("conv_umma_kernel");
     return BVG_OK;
 }

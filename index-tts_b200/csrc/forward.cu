@@ -1,6 +1,7 @@
 // C-ABI entry points for the convolutions and the whole-generator launch plan (reference bigvgan.py:360-386).
 #include "bvg_common.cuh"
 
+#include <cstdlib>
 #include <vector>
 
 namespace bvg {
@@ -54,7 +55,8 @@ static int convtranspose1d(int precision, const void* x, const void* w, const fl
 struct Plan {
     int64_t B, T_mel, E;  // E = max over stages of B*T_i*C_i
     size_t op_es;         // bytes per MMA-operand element
-    size_t off_mel, off_pre, off_x, off_r, off_a, off_y1, off_sum, off_sumop, total;
+    size_t off_mel, off_pre, off_x, off_sum, off_sumop, total;
+    size_t off_r[BVG_MAX_KERNELS], off_a[BVG_MAX_KERNELS], off_y1[BVG_MAX_KERNELS];  // per AMP block (they run concurrently)
 };
 
 static size_t align256(size_t v) { return (v + 255) & ~size_t(255); }
@@ -110,13 +112,53 @@ static int make_plan(const bvg_model_desc* m, int64_t B, int64_t T_mel, Plan* pl
     pl->off_mel = o;   o += align256((size_t)B * T_mel * m->num_mels * pl->op_es);
     pl->off_pre = o;   o += align256((size_t)B * T_mel * m->upsample_initial_channel * pl->op_es);
     pl->off_x = o;     o += align256((size_t)E * 4);
-    pl->off_r = o;     o += align256((size_t)E * 4);
-    pl->off_a = o;     o += align256((size_t)E * pl->op_es);
-    pl->off_y1 = o;    o += align256((size_t)E * 4);
     pl->off_sum = o;   o += align256((size_t)E * 4);
     pl->off_sumop = o; o += align256((size_t)E * pl->op_es);
+    for (int j = 0; j < m->num_kernels; ++j) {
+        pl->off_r[j] = o;  o += align256((size_t)E * 4);
+        pl->off_a[j] = o;  o += align256((size_t)E * pl->op_es);
+        pl->off_y1[j] = o; o += align256((size_t)E * pl->op_es);
+    }
     pl->total = o;
     return BVG_OK;
+}
+
+// ---- concurrent AMP blocks -----------------------------------------------------------------------------------
+// The num_kernels AMP blocks of a stage read the same input and are independent until their last conv, so they are
+// launched on separate streams: the tensor-pipe-bound convs of one block overlap the FP32-pipe-bound Activation1d
+// kernels of another.  The auxiliary streams / events are host-side handles cached per host thread and device (no
+// device memory, no cross-thread sharing); everything is forked from and joined back into the caller's stream, so
+// the caller still sees ordinary stream semantics (and stream capture works).
+struct AuxStreams {
+    int dev = -1;
+    cudaStream_t s[BVG_MAX_KERNELS - 1] = {};
+    cudaEvent_t fork = nullptr, last[BVG_MAX_KERNELS] = {};
+    bool ok = false;
+};
+
+static AuxStreams* aux_streams() {
+    static thread_local AuxStreams cache[8];
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return nullptr;
+    AuxStreams& a = cache[dev & 7];
+    if (a.ok && a.dev == dev) return &a;
+    if (a.ok) return nullptr;  // slot taken by another device: run serially
+    a.dev = dev;
+    bool good = cudaEventCreateWithFlags(&a.fork, cudaEventDisableTiming) == cudaSuccess;
+    for (int i = 0; good && i < BVG_MAX_KERNELS - 1; ++i)
+        good = cudaStreamCreateWithFlags(&a.s[i], cudaStreamNonBlocking) == cudaSuccess;
+    for (int i = 0; good && i < BVG_MAX_KERNELS; ++i)
+        good = cudaEventCreateWithFlags(&a.last[i], cudaEventDisableTiming) == cudaSuccess;
+    a.ok = good;
+    return good ? &a : nullptr;
+}
+
+static int concurrency_requested() {
+    static const int v = []() {
+        const char* e = getenv("BVG_STREAMS");
+        return (e != nullptr && e[0] == '1' && e[1] == 0) ? 0 : 1;
+    }();
+    return v;
 }
 
 }  // namespace bvg
@@ -164,9 +206,8 @@ extern "C" int bvg_forward(const bvg_model_desc* m, const float* mel, int64_t me
     void* mel_nlc = ws + pl.off_mel;
     void* pre = ws + pl.off_pre;
     float* X = reinterpret_cast<float*>(ws + pl.off_x);
-    float* R = reinterpret_cast<float*>(ws + pl.off_r);
-    void* A = ws + pl.off_a;
-    void* Y1 = ws + pl.off_y1;
+    // profiling keeps the plan on one stream so that every event pair brackets exactly one kernel
+    AuxStreams* aux = (g_prof == nullptr && concurrency_requested() && m->num_kernels > 1) ? aux_streams() : nullptr;
     float* SUM = reinterpret_cast<float*>(ws + pl.off_sum);
     void* SUMOP = ws + pl.off_sumop;
 
@@ -209,7 +250,15 @@ extern "C" int bvg_forward(const bvg_model_desc* m, const float* mel, int64_t me
         T *= u;
         C /= 2;
         const bool last_stage = (i + 1 == m->num_stages);
+        if (aux) {
+            BVG_CUDA(cudaEventRecord(aux->fork, st));
+            for (int j = 1; j < m->num_kernels; ++j) BVG_CUDA(cudaStreamWaitEvent(aux->s[j - 1], aux->fork, 0));
+        }
         for (int j = 0; j < m->num_kernels; ++j) {
+            cudaStream_t sj = (aux && j > 0) ? aux->s[j - 1] : st;
+            float* R = reinterpret_cast<float*>(ws + pl.off_r[j]);
+            void* A = ws + pl.off_a[j];
+            void* Y1 = ws + pl.off_y1[j];
             const float* xr = X;  // residual stream of this block (bigvgan.py:132-141)
             for (int l = 0; l < m->num_dilations; ++l) {
                 const bvg_conv_desc& c1 = m->convs1[i][j][l];
@@ -219,54 +268,59 @@ extern "C" int bvg_forward(const bvg_model_desc* m, const float* mel, int64_t me
                 const double rows = (double)B * T;
                 const double act_flops = 62.0 * rows * C, act_bytes = 2.0 * es * rows * C + 8.0 * C;
                 {
-                    ProfScope ps(BVG_K_ACT, i, C, C, 0, 0, B * T, act_flops, act_bytes, st);
-                    rc = activation1d_nlc(xr, BVG_F32, A, op_dt, a1.alpha_log, a1.beta_log, B, T, C, precise, st);
+                    ProfScope ps(BVG_K_ACT, i, C, C, 0, 0, B * T, act_flops, act_bytes, sj);
+                    rc = activation1d_nlc(xr, BVG_F32, A, op_dt, a1.alpha_log, a1.beta_log, B, T, C, precise, sj);
                 }
                 if (rc != BVG_OK) return rc;
                 // xt between c1 and a2 is an intermediate (not the residual stream): operand dtype (bf16 in TC mode;
                 // costs ~1.2 dB of the 43.8 dB budget, tools/emulate_bf16_plan.py)
                 {
                     ProfScope ps(BVG_K_CONV1D, i, C, C, c1.k, c1.dilation, B * T, conv_flops(C, C, c1.k, rows),
-                                 conv_bytes(C, C, c1.k, rows, false), st);
+                                 conv_bytes(C, C, c1.k, rows, false), sj);
                     rc = conv1d(prec, A, c1.w, c1.bias, nullptr, nullptr, tc ? nullptr : reinterpret_cast<float*>(Y1),
-                                tc ? Y1 : nullptr, B, T, C, C, c1.k, c1.dilation, 1.0f, st);
+                                tc ? Y1 : nullptr, B, T, C, C, c1.k, c1.dilation, 1.0f, sj);
                 }
                 if (rc != BVG_OK) return rc;
                 {
-                    ProfScope ps(BVG_K_ACT, i, C, C, 0, 0, B * T, act_flops, act_bytes, st);
-                    rc = activation1d_nlc(Y1, op_dt, A, op_dt, a2.alpha_log, a2.beta_log, B, T, C, precise, st);
+                    ProfScope ps(BVG_K_ACT, i, C, C, 0, 0, B * T, act_flops, act_bytes, sj);
+                    rc = activation1d_nlc(Y1, op_dt, A, op_dt, a2.alpha_log, a2.beta_log, B, T, C, precise, sj);
                 }
                 if (rc != BVG_OK) return rc;
                 ProfScope ps(BVG_K_CONV1D, i, C, C, c2.k, 1, B * T, conv_flops(C, C, c2.k, rows),
-                             conv_bytes(C, C, c2.k, rows, true), st);
+                             conv_bytes(C, C, c2.k, rows, true), sj);
                 const bool last = (l + 1 == m->num_dilations);
                 if (!last) {
                     // x = xt + x
-                    rc = conv1d(prec, A, c2.w, c2.bias, xr, nullptr, R, nullptr, B, T, C, C, c2.k, 1, 1.0f, st);
+                    rc = conv1d(prec, A, c2.w, c2.bias, xr, nullptr, R, nullptr, B, T, C, C, c2.k, 1, 1.0f, sj);
                     xr = R;
                 } else {
-                    // xs (+)= block output; x = xs / num_kernels (bigvgan.py:369-375) folded into the epilogue.
-                    // The last block of a stage also emits the operand-dtype copy the next transposed conv reads.
+                    // xs (+)= block output; x = xs / num_kernels (bigvgan.py:369-375) folded into the epilogue: the
+                    // blocks' last convs accumulate into SUM one after the other (event chain).  The last block of a
+                    // stage also emits the operand-dtype copy the next transposed conv reads.
+                    if (aux && j > 0) BVG_CUDA(cudaStreamWaitEvent(sj, aux->last[j - 1], 0));
                     const bool emit_op = tc && !last_stage && (j + 1 == m->num_kernels);
                     rc = conv1d(prec, A, c2.w, c2.bias, xr, j > 0 ? SUM : nullptr, SUM, emit_op ? SUMOP : nullptr, B, T, C, C,
-                                c2.k, 1, inv_nk, st);
+                                c2.k, 1, inv_nk, sj);
+                    if (aux && rc == BVG_OK) BVG_CUDA(cudaEventRecord(aux->last[j], sj));
                 }
                 if (rc != BVG_OK) return rc;
             }
         }
+        if (aux) BVG_CUDA(cudaStreamWaitEvent(st, aux->last[m->num_kernels - 1], 0));  // join
         stage_in = tc ? SUMOP : static_cast<const void*>(SUM);
     }
     // activation_post -> conv_post -> clamp / tanh (bigvgan.py:378-384), fp32 in both modes
     {
         const double rows = (double)B * T;
         ProfScope ps(BVG_K_ACT, -1, C, C, 0, 0, B * T, 62.0 * rows * C, 2.0 * es * rows * C + 8.0 * C, st);
+        float* R = reinterpret_cast<float*>(ws + pl.off_r[0]);
         rc = activation1d_nlc(SUM, BVG_F32, R, BVG_F32, m->act_post.alpha_log, m->act_post.beta_log, B, T, C, precise, st);
     }
     if (rc != BVG_OK) return rc;
     const bvg_conv_desc& cp = m->conv_post;
     BVG_REQUIRE(cp.cout == 1 && cp.cin == C, BVG_ERR_UNSUPPORTED, "conv_post must map %d channels to 1", C);
     ProfScope ps(BVG_K_POST, -1, C, 1, cp.k, 1, B * T, 2.0 * C * cp.k * (double)B * T, es * (double)B * T * (C + 1.0), st);
-    return bvg_conv_post_fwd(R, static_cast<const float*>(cp.w), cp.bias, wav, B, T, C, cp.k, m->use_tanh_at_final, stream);
+    return bvg_conv_post_fwd(reinterpret_cast<const float*>(ws + pl.off_r[0]), static_cast<const float*>(cp.w), cp.bias, wav, B, T, C, cp.k, m->use_tanh_at_final, stream);
 }
 
 extern "C" int bvg_forward_profile(const bvg_model_desc* m, const float* mel, int64_t mel_stride_b, int64_t mel_stride_c,

@@ -1,4 +1,4 @@
-OUT=gpurun_out/r01c; mkdir -p $OUT
+OUT=gpurun_out/${1:-r01c}; mkdir -p $OUT
 for cfg in "24 220672 11 1 1" "96 55168 11 1 1" "24 220672 3 1 0"; do
   tag=$(echo $cfg | tr ' ' '_')
   C1="python tools/run_one.py conv $cfg"
