@@ -79,6 +79,7 @@ SIGNATURES = {
     "bvg_forward": (c_int, [C.POINTER(ModelDesc), c_vp, c_i64, c_i64, c_vp, c_i64, c_i64, c_vp, c_sz, c_vp]),
     "bvg_forward_profile": (c_int, [C.POINTER(ModelDesc), c_vp, c_i64, c_i64, c_vp, c_i64, c_i64, c_vp, c_sz, c_vp,
                                     C.POINTER(LaunchRecord), c_int, C.POINTER(c_int)]),
+    "bvg_debug_conv_trace": (None, [c_vp, c_int]),
 }
 
 _lock = threading.Lock()

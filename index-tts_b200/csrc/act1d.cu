@@ -258,16 +258,23 @@ struct ActTmaParams {
     uint32_t tx_bytes;     // nsegs * 7 * row_bytes
 };
 
+// Slab reads use explicit shared-space loads on a 32-bit address (the aligned dynamic-smem pointer is otherwise demoted
+// to generic LD by the compiler).
 template <typename T>
 struct SmemPair;
 template <>
 struct SmemPair<float> {
-    static __device__ __forceinline__ float2 load(const uint8_t* p) { return *reinterpret_cast<const float2*>(p); }
+    static __device__ __forceinline__ float2 load(uint32_t a) {
+        float2 v;
+        asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(a));
+        return v;
+    }
 };
 template <>
 struct SmemPair<__nv_bfloat16> {
-    static __device__ __forceinline__ float2 load(const uint8_t* p) {
-        const unsigned int raw = *reinterpret_cast<const unsigned int*>(p);
+    static __device__ __forceinline__ float2 load(uint32_t a) {
+        unsigned int raw;
+        asm volatile("ld.shared.b32 %0, [%1];" : "=r"(raw) : "r"(a));
         return make_float2(__uint_as_float(raw << 16), __uint_as_float(raw & 0xffff0000u));
     }
 };
@@ -291,6 +298,7 @@ act1d_nlc_tma_kernel(const __grid_constant__ CUtensorMap map_x, TOut* __restrict
     }
     __syncthreads();
     const int n_slabs = p.nbody + 1;
+    const uint32_t smem_base = smem_u32(smem);
     int st = 0;
     uint32_t ph = 0;
 
@@ -345,12 +353,12 @@ act1d_nlc_tma_kernel(const __grid_constant__ CUtensorMap map_x, TOut* __restrict
         e.n_out = static_cast<int>(min(static_cast<int64_t>(L), T - t0));
         e.first_seg = (t0 == 0);
 
-        float2 xw[7], ve[7], vo[7], cur[7];
+        float2 xw[7], ve[7], vo[7], cur[7], nxt[7];
         float2 vlast = splat(0.f), xlast = splat(0.f);
         // slab 0: rows t0-7 .. t0-1; the window starts with rows t0-6 .. t0-1
         mbar_wait(&full[st], ph);
         {
-            const uint8_t* sp = smem + st * p.stage_bytes + my_off;
+            const uint32_t sp = smem_base + st * p.stage_bytes + my_off;
 #pragma unroll
             for (int j = 0; j < 6; ++j) xw[j] = SmemPair<TIn>::load(sp + (j + 1) * p.row_bytes);
         }
@@ -359,18 +367,24 @@ act1d_nlc_tma_kernel(const __grid_constant__ CUtensorMap map_x, TOut* __restrict
         if (++st == p.stages) { st = 0; ph ^= 1; }
 #pragma unroll
         for (int s = 0; s < 7; ++s) ve[s] = vo[s] = splat(0.f);
-
-#pragma unroll 1
-        for (int body = 0; body < p.nbody; ++body) {
+        // the slab of body b+1 is read into registers before body b is computed, so its mbarrier wait and shared-memory
+        // latency sit under ~350 instructions of FFMA2 / MUFU work
+        auto fetch = [&](float2 (&dst)[7]) {
             mbar_wait(&full[st], ph);
-            {
-                const uint8_t* sp = smem + st * p.stage_bytes + my_off;
+            const uint32_t sp = smem_base + st * p.stage_bytes + my_off;
 #pragma unroll
-                for (int s = 0; s < 7; ++s) cur[s] = SmemPair<TIn>::load(sp + s * p.row_bytes);
-            }
+            for (int s = 0; s < 7; ++s) dst[s] = SmemPair<TIn>::load(sp + s * p.row_bytes);
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty[st]);
             if (++st == p.stages) { st = 0; ph ^= 1; }
+        };
+        fetch(nxt);
+
+#pragma unroll 1
+        for (int body = 0; body < p.nbody; ++body) {
+#pragma unroll
+            for (int s = 0; s < 7; ++s) cur[s] = nxt[s];
+            if (body + 1 < p.nbody) fetch(nxt);
             if (!active) continue;
             const int g0 = 7 * body;
             if (edge_path) {

@@ -79,8 +79,18 @@ struct ConvUmmaParams {
     // per-warp swizzled smem tiles and bulk tensor stores
     int has_res, has_acc, has_y32, has_y16;
     int ld_stages;     // residual/accum chunk ring depth (<= UMMA_MAX_STAGES)
+    unsigned long long* trace;  // developer timeline buffer (bvg_debug_conv_trace) or null
+    int trace_n;
+    uint32_t bias_smem;  // bytes of the zero-padded bias copy in shared memory (0: read the bias from global memory)
+    int dbg;           // developer timing experiments (BVG_CONV_DBG): 1 = no output stores, 2 = no A loads, 4 = no chunk loads
     float out_scale;
 };
+
+// Developer timeline: event e of pipeline role `slot` at the role's i-th tile (CTA 0 only).
+__device__ __forceinline__ void trace_ev(const ConvUmmaParams& p, int slot, uint32_t i) {
+    if (p.trace != nullptr && blockIdx.x == 0 && i < static_cast<uint32_t>(p.trace_n))
+        p.trace[static_cast<size_t>(slot) * p.trace_n + i] = clock64();
+}
 
 // Tile index -> (n tile, m tile, batch item), 32-bit arithmetic (total_tiles < 2^31 is checked by the launcher).
 struct TileCoord {
@@ -99,6 +109,23 @@ __device__ __forceinline__ TileCoord decode_tile(uint32_t tile, uint32_t n_tiles
     c.b = static_cast<int>(b);
     return c;
 }
+// A role's walk over its tiles (first, first + step, ...): the two divisions are paid once, every further tile is a
+// mixed-radix add with carries (a tile is only ~1000 cycles for the small-channel layers, two 32-bit divisions per
+// tile and role were a measurable part of it).
+struct TileWalker {
+    TileCoord c, d;
+    int n_tiles, m_tiles;
+    __device__ __forceinline__ TileWalker(uint32_t first, uint32_t step, uint32_t n_tiles_, uint32_t m_tiles_)
+        : c(decode_tile(first, n_tiles_, m_tiles_)), d(decode_tile(step, n_tiles_, m_tiles_)),
+          n_tiles(static_cast<int>(n_tiles_)), m_tiles(static_cast<int>(m_tiles_)) {}
+    __device__ __forceinline__ void next() {
+        c.nt += d.nt;
+        c.mt += d.mt;
+        c.b += d.b;
+        if (c.nt >= n_tiles) { c.nt -= n_tiles; ++c.mt; }
+        if (c.mt >= m_tiles) { c.mt -= m_tiles; ++c.b; }
+    }
+};
 
 // tcgen05.mma with the 64-bit shared-memory descriptors assembled from a 32-bit cursor (start-address field, i.e.
 // byte address >> 4) and the constant upper half: advancing an operand is one 32-bit uniform add.
@@ -149,9 +176,11 @@ __device__ __forceinline__ void umma_issue_loop(const ConvUmmaParams& p, uint32_
     int sa = 0, sb = 0;
     uint32_t acc = 0, pa = 0, pb = 0, pacc = 0;
     if (STAT) mbar_wait(&b_full[0], 0);
-    for (uint32_t tile = blockIdx.x + group * gridDim.x; tile < total; tile += ng * gridDim.x) {
+    uint32_t it = 0;
+    for (uint32_t tile = blockIdx.x + group * gridDim.x; tile < total; tile += ng * gridDim.x, ++it) {
         mbar_wait(&acc_empty[acc], pacc ^ 1);
         tc_fence_after_sync();
+        if (leader) trace_ev(p, 1 + 6 * group, it);
         const uint32_t d_tmem = tmem_base + (2 * group + acc) * n_tile;
         uint32_t accumulate = 0;
         uint32_t w_d = sB_d;  // stationary weight cursor
@@ -161,6 +190,7 @@ __device__ __forceinline__ void umma_issue_loop(const ConvUmmaParams& p, uint32_
             const bool k2 = k_steps > 1, k3 = k_steps > 2, k4 = k_steps > 3;
             mbar_wait(&a_full[sa], pa);
             tc_fence_after_sync();
+            if (leader && kb == 0) trace_ev(p, 2 + 6 * group, it);
             uint32_t a_d = sA_d + sa * a_stage_d;
 #pragma unroll 1
             for (int j = 0; j < taps; ++j) {
@@ -190,6 +220,7 @@ __device__ __forceinline__ void umma_issue_loop(const ConvUmmaParams& p, uint32_
             if (++sa == a_stages) { sa = 0; pa ^= 1; }
         }
         if (leader) umma_commit(&acc_full[acc]);
+        if (leader) trace_ev(p, 3 + 6 * group, it);
         acc ^= 1;
         if (acc == 0) pacc ^= 1;
     }
@@ -210,7 +241,8 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
     const int n_ld = p.has_res + p.has_acc;
     uint8_t* sSt32 = sLd + p.ld_stages * n_ld * EPI_LD_TILE_BYTES;
     uint8_t* sSt16 = sSt32 + (p.has_y32 ? p.ng * 4 * 2 * EPI_ST32_TILE_BYTES : 0);
-    uint64_t* bars = reinterpret_cast<uint64_t*>(sSt16 + (p.has_y16 ? p.ng * 4 * 2 * EPI_ST16_TILE_BYTES : 0));
+    float* sBias = reinterpret_cast<float*>(sSt16 + (p.has_y16 ? p.ng * 4 * 2 * EPI_ST16_TILE_BYTES : 0));
+    uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(sBias) + p.bias_smem);
     uint64_t* a_full = bars;
     uint64_t* a_empty = bars + UMMA_MAX_STAGES;
     uint64_t* b_full = bars + 2 * UMMA_MAX_STAGES;   // [0] doubles as "weights resident" in stationary mode
@@ -224,6 +256,11 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
 
+    if (p.trace != nullptr && threadIdx.x == 0 && gridDim.x <= static_cast<unsigned>(p.trace_n)) {
+        unsigned long long ns;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns));
+        p.trace[13 * static_cast<size_t>(p.trace_n) + blockIdx.x] = ns;  // CTA start (ns)
+    }
     if (threadIdx.x == 0) {
         tma_prefetch_desc(&map_x);
         tma_prefetch_desc(&map_w);
@@ -234,6 +271,10 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
         }
         for (int i = 0; i < 4; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 4); }
         fence_barrier_init();
+    }
+    if (p.bias_smem) {
+        const int nb = static_cast<int>(p.bias_smem / 4);
+        for (int i = threadIdx.x; i < nb; i += blockDim.x) sBias[i] = i < p.cout_phase ? __ldg(p.bias + i) : 0.0f;
     }
     if (warp == 1) tmem_alloc(tmem_ptr, p.tmem_cols);
     tc_fence_before_sync();
@@ -265,9 +306,10 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
         // per-group cursors into the groups' A sub-rings (tiles alternate between the groups)
         const int a_per = p.a_stages / p.ng;
         int sa = 0, sa_other = 0, sb = 0, g = 0;
-        uint32_t pa = 0, pa_other = 0, pb = 0;
-        for (uint32_t tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-            const TileCoord tc = decode_tile(tile, n_tiles, m_tiles);
+        uint32_t pa = 0, pa_other = 0, pb = 0, it = 0;
+        TileWalker tw(blockIdx.x, gridDim.x, n_tiles, m_tiles);
+        for (uint32_t tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it, tw.next()) {
+            const TileCoord tc = tw.c;
             const int nt = tc.nt, mt = tc.mt, b = tc.b;
             const int slot0 = g * a_per;
             const int phase = nt / p.tiles_per_phase;
@@ -275,9 +317,14 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
             const int row0 = mt * UMMA_BLOCK_M + p.tap_base[phase];
             for (int kb = 0; kb < k_blocks; ++kb) {
                 mbar_wait(&a_empty[slot0 + sa], pa ^ 1);
+                if (kb == 0 && lane == 0) trace_ev(p, 0, it);
                 if (elect_one()) {
-                    mbar_arrive_expect_tx(&a_full[slot0 + sa], p.a_stage_bytes);
-                    tma_load_3d(sA + (slot0 + sa) * p.a_stage_bytes, &map_x, &a_full[slot0 + sa], kb * UMMA_BLOCK_K, row0, b);
+                    if (p.dbg & 2) {
+                        mbar_arrive(&a_full[slot0 + sa]);
+                    } else {
+                        mbar_arrive_expect_tx(&a_full[slot0 + sa], p.a_stage_bytes);
+                        tma_load_3d(sA + (slot0 + sa) * p.a_stage_bytes, &map_x, &a_full[slot0 + sa], kb * UMMA_BLOCK_K, row0, b);
+                    }
                 }
                 if (++sa == a_per) { sa = 0; pa ^= 1; }
                 if (!p.stationary) {
@@ -316,8 +363,9 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
             const int ld_per = p.ld_stages / p.ng;
             int s = 0, s_other = 0, g = 0;
             uint32_t ps = 0, ps_other = 0;
-            for (uint32_t tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-                const TileCoord tc = decode_tile(tile, n_tiles, m_tiles);
+            TileWalker tw(blockIdx.x, gridDim.x, n_tiles, m_tiles);
+            for (uint32_t tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, tw.next()) {
+                const TileCoord tc = tw.c;
                 const int nt = tc.nt, t0 = tc.mt * UMMA_BLOCK_M, b = tc.b;
                 const int phase = nt / p.tiles_per_phase;
                 const int c0 = (nt % p.tiles_per_phase) * p.n_tile;
@@ -325,7 +373,9 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                 for (int c = 0; c < p.n_tile; c += EPI_CHUNK) {
                     const int slot = slot0 + s;
                     mbar_wait(&ld_empty[slot], ps ^ 1);
-                    if (elect_one()) {
+                    if ((p.dbg & 4) && elect_one()) {
+                        mbar_arrive(&ld_full[slot]);
+                    } else if (elect_one()) {
                         mbar_arrive_expect_tx(&ld_full[slot], n_ld * EPI_LD_TILE_BYTES);
                         uint8_t* dst = sLd + slot * n_ld * EPI_LD_TILE_BYTES;
                         if (p.has_res) tma_load_4d(dst, &map_res, &ld_full[slot], c0 + c, phase, t0, b);
@@ -360,14 +410,18 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
         ld_empty += group * ld_per;
         int acc = 0, ls = 0, ob = 0;
         uint32_t pacc = 0, pls = 0;
-        for (uint32_t tile = blockIdx.x + group * gridDim.x; tile < total_tiles; tile += p.ng * gridDim.x) {
-            const TileCoord tc = decode_tile(tile, n_tiles, m_tiles);
+        const bool tracer = (q == 0 && lane == 0);
+        uint32_t it = 0;
+        TileWalker tw(blockIdx.x + group * gridDim.x, p.ng * gridDim.x, n_tiles, m_tiles);
+        for (uint32_t tile = blockIdx.x + group * gridDim.x; tile < total_tiles; tile += p.ng * gridDim.x, ++it, tw.next()) {
+            const TileCoord tc = tw.c;
             const int nt = tc.nt, t0 = tc.mt * UMMA_BLOCK_M, b = tc.b;
             const int phase = nt / p.tiles_per_phase;
             const int c0 = (nt % p.tiles_per_phase) * p.n_tile;  // channel offset inside the phase
 
             mbar_wait(&acc_full[acc], pacc);
             tc_fence_after_sync();
+            if (tracer) trace_ev(p, 4 + 6 * group, it);
             const uint32_t t_addr = tmem_base + ((static_cast<uint32_t>(q) * 32u) << 16) + (2 * group + acc) * p.n_tile;
             for (int c = 0; c < p.n_tile; c += EPI_CHUNK) {
                 const int width = min(EPI_CHUNK, p.n_tile - c);  // 32 or 16
@@ -390,14 +444,24 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                     tc_fence_before_sync();
                     __syncwarp();
                     if (lane == 0) mbar_arrive(&acc_empty[acc]);
+                    if (tracer) trace_ev(p, 5 + 6 * group, it);
                 }
                 if (p.bias) {
                     const int chb = c0 + c;
+                    if (p.bias_smem) {  // zero-padded copy in shared memory: broadcast reads, no bounds checks
+                        const float4* bs = reinterpret_cast<const float4*>(sBias + chb);
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) {
-                        if (chb + 4 * j < p.cout_phase) {
-                            const float4 bv = __ldg(reinterpret_cast<const float4*>(p.bias + chb + 4 * j));
+                        for (int j = 0; j < 8; ++j) {
+                            const float4 bv = bs[j];
                             o[4 * j] += bv.x; o[4 * j + 1] += bv.y; o[4 * j + 2] += bv.z; o[4 * j + 3] += bv.w;
+                        }
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            if (chb + 4 * j < p.cout_phase) {
+                                const float4 bv = __ldg(reinterpret_cast<const float4*>(p.bias + chb + 4 * j));
+                                o[4 * j] += bv.x; o[4 * j + 1] += bv.y; o[4 * j + 2] += bv.z; o[4 * j + 3] += bv.w;
+                            }
                         }
                     }
                 }
@@ -411,8 +475,10 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                             o[4 * j] += rv.x; o[4 * j + 1] += rv.y; o[4 * j + 2] += rv.z; o[4 * j + 3] += rv.w;
                         }
                     }
+                    if (p.out_scale != 1.0f) {
 #pragma unroll
-                    for (int e = 0; e < 32; ++e) o[e] *= p.out_scale;
+                        for (int e = 0; e < 32; ++e) o[e] *= p.out_scale;
+                    }
                     if (p.has_acc) {
                         const uint8_t* la = ld + p.has_res * EPI_LD_TILE_BYTES;
 #pragma unroll
@@ -424,7 +490,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                     __syncwarp();
                     if (lane == 0) mbar_arrive(&ld_empty[ls]);
                     if (++ls == ld_per) { ls = 0; pls ^= 1; }
-                } else {
+                } else if (p.out_scale != 1.0f) {
 #pragma unroll
                     for (int e = 0; e < 32; ++e) o[e] *= p.out_scale;
                 }
@@ -453,7 +519,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                 }
                 fence_proxy_async_smem();
                 __syncwarp();
-                if (lane == 0) {
+                if (lane == 0 && !(p.dbg & 1)) {
                     if (p.has_y32) tma_store_4d(&map_y32, st32 + ob * EPI_ST32_TILE_BYTES, c0 + c, phase, t0 + q * 32, b);
                     if (p.has_y16) tma_store_4d(&map_y16, st16 + ob * EPI_ST16_TILE_BYTES, c0 + c, phase, t0 + q * 32, b);
                     tma_store_commit();
@@ -461,12 +527,18 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                 ob ^= 1;
             }
             if (++acc == 2) { acc = 0; pacc ^= 1; }
+            if (tracer) trace_ev(p, 6 + 6 * group, it);
         }
         if (lane == 0) tma_store_wait<0>();
     }
 
     tc_fence_before_sync();
     __syncthreads();
+    if (p.trace != nullptr && threadIdx.x == 0 && gridDim.x <= static_cast<unsigned>(p.trace_n)) {
+        unsigned long long ns;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns));
+        p.trace[14 * static_cast<size_t>(p.trace_n) + blockIdx.x] = ns;  // CTA end (ns)
+    }
     if (warp == 1) {
         tc_fence_after_sync();
         tmem_dealloc(tmem_base, p.tmem_cols);
@@ -512,6 +584,9 @@ static int encode_io_4d(CUtensorMap* map, const void* ptr, bool bf16, uint64_t c
     BVG_REQUIRE(r == CUDA_SUCCESS, BVG_ERR_CUDA, "cuTensorMapEncodeTiled(%s) failed with CUresult %d", what, (int)r);
     return BVG_OK;
 }
+
+static unsigned long long* g_conv_trace = nullptr;
+static int g_conv_trace_n = 0;
 
 // Shared-memory budget of one CTA.  Below the 227 KB maximum an Activation1d CTA of another AMP block can be resident
 // on the same SM (forward.cu runs the blocks on separate streams), trading pipeline depth for FP32/tensor overlap.
@@ -563,6 +638,12 @@ int conv_umma_launch(const void* x, const void* w_packed, const float* bias, con
     p.a_stage_bytes = (uint32_t)round_up((int64_t)a_rows * 128, 1024);
     p.b_stage_bytes = (uint32_t)round_up((int64_t)p.n_tile * 128, 1024);
     p.ng = 1;
+    p.trace = g_conv_trace;
+    p.trace_n = g_conv_trace_n;
+    {
+        static const int dbg_env = []() { const char* e = getenv("BVG_CONV_DBG"); return e ? atoi(e) : 0; }();
+        p.dbg = dbg_env;
+    }
     p.has_res = residual != nullptr; p.has_acc = accum != nullptr;
     p.has_y32 = y_f32 != nullptr; p.has_y16 = y_bf16 != nullptr;
     const int n_ld = p.has_res + p.has_acc;
@@ -575,12 +656,14 @@ int conv_umma_launch(const void* x, const void* w_packed, const float* bias, con
     // dual pipeline when the weights are small enough to be stationary and four accumulators fit TMEM
     static const int ng_env = []() { const char* e = getenv("BVG_CONV_GROUPS"); return e ? atoi(e) : 0; }();
     if (ng_env != 1 && 4 * p.n_tile <= 512 && w_all <= 96 * 1024) p.ng = 2;
+    // bias copy in shared memory (zero-padded by one epilogue chunk so the chunk reads need no bounds checks)
+    p.bias_smem = (bias != nullptr && cout_phase <= 768) ? (uint32_t)round_up((cout_phase + EPI_CHUNK) * 4, 128) : 0u;
     bool planned = false;
     uint32_t st_bytes = 0;
     for (int ng_try = p.ng; ng_try >= 1 && !planned; --ng_try) {
         p.ng = ng_try;
         st_bytes = p.ng * ((p.has_y32 ? 8 * EPI_ST32_TILE_BYTES : 0) + (p.has_y16 ? 8 * EPI_ST16_TILE_BYTES : 0));
-        const uint32_t fixed = 1024 + 1024 + st_bytes;
+        const uint32_t fixed = 1024 + 1024 + st_bytes + p.bias_smem;
         // best effort: plan inside the (possibly reduced) budget first, fall back to the full 227 KB when a layer needs it
         const int64_t budgets[2] = {conv_smem_budget(), 227 * 1024};
         for (int attempt = 0; attempt < 2 && !planned; ++attempt) {
@@ -617,7 +700,9 @@ int conv_umma_launch(const void* x, const void* w_packed, const float* bias, con
                 }
             }
         }
-        if (planned && p.ng == 2 && !p.stationary) planned = false;  // the dual pipeline needs resident weights
+        // the dual pipeline needs resident weights and at least two A stages per group (measured: with one stage per group
+        // it is slower than the single pipeline with its deeper rings, gpurun_out/r01o)
+        if (planned && p.ng == 2 && (!p.stationary || p.a_stages < 4)) planned = false;
     }
     BVG_REQUIRE(planned, BVG_ERR_UNSUPPORTED, "conv_umma: tile does not fit shared memory");
     BVG_REQUIRE(p.ng == 1 || p.stationary, BVG_ERR_UNSUPPORTED, "conv_umma: dual pipeline planned without stationary weights");
@@ -627,7 +712,7 @@ int conv_umma_launch(const void* x, const void* w_packed, const float* bias, con
         p.tmem_cols = tm;
     }
     const uint32_t smem_bytes = p.a_stages * p.a_stage_bytes + (p.stationary ? p.w_bytes : p.b_stages * p.b_stage_bytes) +
-                                p.ld_stages * n_ld * EPI_LD_TILE_BYTES + st_bytes + 1024 + 1024;
+                                p.ld_stages * n_ld * EPI_LD_TILE_BYTES + st_bytes + p.bias_smem + 1024 + 1024;
     BVG_REQUIRE(smem_bytes <= 227 * 1024, BVG_ERR_UNSUPPORTED, "conv_umma: %u bytes of shared memory needed", smem_bytes);
 
     CUtensorMap map_x, map_w, map_res, map_acc, map_y32, map_y16;
@@ -664,3 +749,8 @@ int conv_umma_launch(const void* x, const void* w_packed, const float* bias, con
 }
 
 }  // namespace bvg
+
+extern "C" void bvg_debug_conv_trace(void* buf, int n_tiles) {
+    bvg::g_conv_trace = static_cast<unsigned long long*>(buf);
+    bvg::g_conv_trace_n = buf ? n_tiles : 0;
+}
