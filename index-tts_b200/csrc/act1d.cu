@@ -485,7 +485,10 @@ __global__ void __launch_bounds__(NCL_THREADS)
 act1d_ncl_kernel(const TIO* __restrict__ x, TIO* __restrict__ y, const float* __restrict__ alpha,
                  const float* __restrict__ beta, int64_t C, int64_t T, int64_t stride_b, int64_t stride_c,
                  int vec_store_ok) {
-    __shared__ __align__(128) TIO tile[NCL_SMEM_ELEMS];
+    // also reused as the fp32 output staging tile (NCL_TILE + NCL_TILE/32 words) on the unaligned-row path
+    constexpr int kTileElems = (NCL_TILE + NCL_TILE / 32) * 4 / (int)sizeof(TIO) > NCL_SMEM_ELEMS
+                                   ? (NCL_TILE + NCL_TILE / 32) * 4 / (int)sizeof(TIO) : NCL_SMEM_ELEMS;
+    __shared__ __align__(128) TIO tile[kTileElems];
     __shared__ __align__(8) uint64_t bar;
     const int64_t c = blockIdx.y, b = blockIdx.z;
     const int64_t t0 = (int64_t)blockIdx.x * NCL_TILE;
@@ -510,19 +513,30 @@ act1d_ncl_kernel(const TIO* __restrict__ x, TIO* __restrict__ y, const float* __
     mbar_wait(&bar, 0);
 
     const int64_t i0 = t0 + (int64_t)threadIdx.x * NCL_PER_THREAD;
-    if (i0 >= T) return;
+    const bool active = i0 < T;  // no early return: every thread reaches the staging barrier below
 
     // xr[j] = x[cl(i0 - 8 + j)]
     float xr[32];
-    if (delta == 0 && i0 - 8 >= lo && i0 + 24 <= hi) {
-        NclIO<TIO>::load32(tile, static_cast<int>(i0 - 8 - lo), xr);
+    if (active) {
+        if (i0 - 8 >= lo && i0 + 24 <= hi) {  // interior thread: no clamping
+            const int base = delta + static_cast<int>(i0 - 8 - lo);
+            if (delta == 0) {
+                NclIO<TIO>::load32(tile, base, xr);
+            } else {  // row not 16-byte aligned (odd T): scalar shared-memory reads, still no index arithmetic per element
+#pragma unroll
+                for (int j = 0; j < 32; ++j) xr[j] = NclIO<TIO>::get(tile, base + j);
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+                int64_t idx = i0 - 8 + j;
+                idx = idx < 0 ? 0 : (idx >= T ? T - 1 : idx);
+                xr[j] = NclIO<TIO>::get(tile, delta + static_cast<int>(idx - lo));
+            }
+        }
     } else {
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-            int64_t idx = i0 - 8 + j;
-            idx = idx < 0 ? 0 : (idx >= T ? T - 1 : idx);
-            xr[j] = NclIO<TIO>::get(tile, delta + static_cast<int>(idx - lo));
-        }
+        for (int j = 0; j < 32; ++j) xr[j] = 0.f;
     }
 
     const float e0 = 2.f * BVG_F0, e1 = 2.f * BVG_F1, e2 = 2.f * BVG_F2, e3 = 2.f * BVG_F3, e4 = 2.f * BVG_F4,
@@ -565,13 +579,34 @@ act1d_ncl_kernel(const TIO* __restrict__ x, TIO* __restrict__ y, const float* __
         out[q] = r + acc.y + hoisted_c;
     }
     TIO* yrow = y + (b * C + c) * T + i0;
-    if (vec_store_ok && i0 + NCL_PER_THREAD <= T) {
-        NclIO<TIO>::store16(yrow, out);
-    } else {
+    if (vec_store_ok) {
+        if (active) {
+            if (i0 + NCL_PER_THREAD <= T) {
+                NclIO<TIO>::store16(yrow, out);
+            } else {
 #pragma unroll
-        for (int q = 0; q < NCL_PER_THREAD; ++q)
-            if (i0 + q < T) NclIO<TIO>::store1(yrow + q, out[q]);
+                for (int q = 0; q < NCL_PER_THREAD; ++q)
+                    if (i0 + q < T) NclIO<TIO>::store1(yrow + q, out[q]);
+            }
+        }
+        return;
     }
+    // Rows that are not 16-byte aligned (odd T): per-thread stores would be 16 scattered scalar writes per lane, so the
+    // tile is transposed through shared memory (one pad word per 32 keeps both phases bank-conflict free) and written
+    // with fully coalesced scalar stores.
+    __syncthreads();  // every thread has consumed its part of the input tile
+    float* stage = reinterpret_cast<float*>(tile);
+    if (active) {
+#pragma unroll
+        for (int q = 0; q < NCL_PER_THREAD; ++q) {
+            const int w = threadIdx.x * NCL_PER_THREAD + q;
+            stage[w + (w >> 5)] = out[q];
+        }
+    }
+    __syncthreads();
+    const int n_valid = static_cast<int>(min((int64_t)NCL_TILE, T - t0));
+    TIO* ytile = y + (b * C + c) * T + t0;
+    for (int w = threadIdx.x; w < n_valid; w += NCL_THREADS) NclIO<TIO>::store1(ytile + w, stage[w + (w >> 5)]);
 }
 
 // ------------------------------------------------------------------------------------------------------------

@@ -52,6 +52,8 @@ if N >= 148:
     dur = sorted((int(e - s_), i) for i, (s_, e) in enumerate(zip(st, en)) if s_ > 0)
     print("CTA durations ns: min", dur[0], "median", dur[len(dur) // 2], "max", dur[-1], " kernel span", int(en.max()) - t0,
           " start skew", int(st.max()) - t0)
+    d2 = [int(e - s_) // 1000 for s_, e in zip(st, en)]
+    print("CTA durations us by blockIdx:", d2)
     print("CTA0 role end cycles:", {names[s]: int(t[s][(t[s] > 0).sum() - 1]) - base for s in (0, 3, 6, 9, 12) if (t[s] > 0).sum() > 0})
 print("raw first 12 tiles (cycles from start):")
 for s in range(13):
