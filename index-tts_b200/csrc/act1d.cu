@@ -102,14 +102,20 @@ struct ActEdge {
 };
 
 // One 7-step body: consumes cur[0..6] (rows rel 6+g0 .. 12+g0), produces outputs rel rows g0-6 .. g0.
+// The low-pass runs in TRANSPOSED form: the pair (v[2m], v[2m+1]) produced at a step is scattered into the seven
+// pending outputs y[m-3 .. m+3] (y[i] = sum_k g[k] v[2i+k-5]; v[2m] carries tap 2(m-i)+5, v[2m+1] tap 2(m-i)+6), so
+// the twelve FFMA2 of a step are mutually independent (no 12-deep dependent chain) and only seven accumulators live
+// in registers instead of a 14-entry history of the activated signal.  acc[(s+j+3)%7] holds y[m+j] at step s.
 template <typename TOut, bool PRECISE, bool EDGE, bool FIRST>
-__device__ __forceinline__ void act1d_nlc_body(float2 (&xw)[7], float2 (&ve)[7], float2 (&vo)[7],
-                                               const float2 (&cur)[7], float2& vlast, const SnakeCoef& coef,
-                                               const ActEdge& e, int g0, TOut* __restrict__ yrel, int64_t C) {
+__device__ __forceinline__ void act1d_nlc_body(float2 (&xw)[7], float2 (&acc)[7], const float2 (&cur)[7], float2& vlast,
+                                               const SnakeCoef& coef, const ActEdge& e, int g0, TOut* __restrict__ yrel,
+                                               int64_t C) {
     const float2 E0 = splat(2.f * BVG_F0), E1 = splat(2.f * BVG_F1), E2 = splat(2.f * BVG_F2),
                  E3 = splat(2.f * BVG_F3), E4 = splat(2.f * BVG_F4), E5 = splat(2.f * BVG_F5);
     const float2 G0 = splat(BVG_F0), G1 = splat(BVG_F1), G2 = splat(BVG_F2), G3 = splat(BVG_F3), G4 = splat(BVG_F4),
                  G5 = splat(BVG_F5);
+    // fast mode: the constant term of sin^2 = (1 - cos)/2 passes the unit-DC-gain low-pass unchanged, so it seeds
+    // every accumulator instead of being added per sample
     const float2 hoisted_c = PRECISE ? splat(0.f) : coef.invb;
 #pragma unroll
     for (int s = 0; s < 7; ++s) {
@@ -118,16 +124,16 @@ __device__ __forceinline__ void act1d_nlc_body(float2 (&xw)[7], float2 (&ve)[7],
         const float2 xm3 = xw[(s + 0) % 7], xm2 = xw[(s + 1) % 7], xm1 = xw[(s + 2) % 7], x0 = xw[(s + 3) % 7],
                      xp1 = xw[(s + 4) % 7], xp2 = xw[(s + 5) % 7], xp3 = xw[(s + 6) % 7];
         float2 ue = fmul2(E0, xm3);
-        ue = ffma2(E2, xm2, ue);
-        ue = ffma2(E4, xm1, ue);
-        ue = ffma2(E5, x0, ue);
-        ue = ffma2(E3, xp1, ue);
-        ue = ffma2(E1, xp2, ue);
         float2 uo = fmul2(E1, xm2);
+        ue = ffma2(E2, xm2, ue);
         uo = ffma2(E3, xm1, uo);
+        ue = ffma2(E4, xm1, ue);
         uo = ffma2(E5, x0, uo);
+        ue = ffma2(E5, x0, ue);
         uo = ffma2(E4, xp1, uo);
+        ue = ffma2(E3, xp1, ue);
         uo = ffma2(E2, xp2, uo);
+        ue = ffma2(E1, xp2, ue);
         uo = ffma2(E0, xp3, uo);
         float2 a = snake2<PRECISE>(ue, coef);
         float2 o = snake2<PRECISE>(uo, coef);
@@ -139,27 +145,37 @@ __device__ __forceinline__ void act1d_nlc_body(float2 (&xw)[7], float2 (&ve)[7],
                 vlast = o;
             }
         }
-        ve[s] = a;
-        vo[s] = o;
-        if (EDGE && FIRST && s == 3 && e.first_seg) {  // m == 0: replicate padding on the left: v[0]
-            ve[0] = vo[0] = ve[1] = vo[1] = ve[2] = vo[2] = a;
+        float2& yp3 = acc[(s + 6) % 7];
+        float2& yp2 = acc[(s + 5) % 7];
+        float2& yp1 = acc[(s + 4) % 7];
+        float2& y00 = acc[(s + 3) % 7];
+        float2& ym1 = acc[(s + 2) % 7];
+        float2& ym2 = acc[(s + 1) % 7];
+        float2& ym3 = acc[(s + 0) % 7];
+        if (EDGE && FIRST && s == 3 && e.first_seg) {
+            // m == 0: replicate padding on the left, v[n < 0] = v[0]: the virtual pairs m = -3, -2, -1 are (a, a)
+            const float2 g0a = ffma2(G0, a, hoisted_c);
+            const float2 g12 = splat(BVG_F1 + BVG_F2), g34 = splat(BVG_F3 + BVG_F4);
+            yp2 = g0a;                                     // y[2]: pair -1 tap 0
+            yp1 = ffma2(g12, a, g0a);                      // y[1]: pair -2 tap 0, pair -1 taps 1,2
+            y00 = ffma2(g34, a, ffma2(g12, a, g0a));       // y[0]: pair -3 tap 0, pair -2 taps 1,2, pair -1 taps 3,4
+            // (whatever steps 0..2 scattered into these three from the clamped-x pairs is discarded here)
         }
+        yp3 = ffma2(G0, o, hoisted_c);
+        yp2 = ffma2(G1, a, yp2);
+        yp1 = ffma2(G3, a, yp1);
+        y00 = ffma2(G5, a, y00);
+        ym1 = ffma2(G4, a, ym1);
+        ym2 = ffma2(G2, a, ym2);
+        ym3 = ffma2(G0, a, ym3);
+        yp2 = ffma2(G2, o, yp2);
+        yp1 = ffma2(G4, o, yp1);
+        y00 = ffma2(G5, o, y00);
+        ym1 = ffma2(G3, o, ym1);
+        ym2 = ffma2(G1, o, ym2);
         if (!FIRST || s == 6) {
             const int i = g - 6;  // output row relative to t0
-            float2 acc = fmul2(G0, vo[(s + 1) % 7]);
-            acc = ffma2(G1, ve[(s + 2) % 7], acc);
-            acc = ffma2(G2, vo[(s + 2) % 7], acc);
-            acc = ffma2(G3, ve[(s + 3) % 7], acc);
-            acc = ffma2(G4, vo[(s + 3) % 7], acc);
-            acc = ffma2(G5, ve[(s + 4) % 7], acc);
-            acc = ffma2(G5, vo[(s + 4) % 7], acc);
-            acc = ffma2(G4, ve[(s + 5) % 7], acc);
-            acc = ffma2(G3, vo[(s + 5) % 7], acc);
-            acc = ffma2(G2, ve[(s + 6) % 7], acc);
-            acc = ffma2(G1, vo[(s + 6) % 7], acc);
-            acc = ffma2(G0, ve[s], acc);
-            if (!PRECISE) acc = fadd2(acc, hoisted_c);
-            if (!EDGE || i < e.n_out) PairIO<TOut>::store(yrel + (int64_t)i * C, acc);
+            if (!EDGE || i < e.n_out) PairIO<TOut>::store(yrel + (int64_t)i * C, ym3);
         }
     }
 }
@@ -183,21 +199,21 @@ __device__ __forceinline__ void act1d_nlc_segment(const TIn* __restrict__ xb, TO
     // x window: x[m+j], j=-3..3, lives in xw[(s+j+3)%7] at step s of a 7-step body; pair m in ve/vo[s].
     // Loads run two 7-row bodies (~14 rows, > 1 us of work per warp) ahead of their use: global latency is hidden by
     // the register prefetch queue cur <- nxt <- nxt2 rather than by occupancy (2 CTAs/SM at ~110 registers).
-    float2 xw[7], ve[7], vo[7], cur[7], nxt[7], nxt2[7];
+    float2 xw[7], acc[7], cur[7], nxt[7], nxt2[7];
     float2 vlast = splat(0.f);
 #pragma unroll
     for (int j = 0; j < 6; ++j) xw[j] = ldx(j);
 #pragma unroll
     for (int s = 0; s < 7; ++s) {
         cur[s] = ldx(6 + s);
-        ve[s] = vo[s] = splat(0.f);
+        acc[s] = splat(0.f);
     }
     const int nbody = (L + 6) / 7;
 #pragma unroll
     for (int s = 0; s < 7; ++s) nxt[s] = nbody > 1 ? ldx(13 + s) : splat(0.f);
 #pragma unroll
     for (int s = 0; s < 7; ++s) nxt2[s] = nbody > 2 ? ldx(20 + s) : splat(0.f);
-    act1d_nlc_body<TOut, PRECISE, EDGE, true>(xw, ve, vo, cur, vlast, coef, e, 0, yrel, C);
+    act1d_nlc_body<TOut, PRECISE, EDGE, true>(xw, acc, cur, vlast, coef, e, 0, yrel, C);
 #pragma unroll 1
     for (int body = 1; body < nbody; ++body) {
         const int g0 = 7 * body;
@@ -207,7 +223,7 @@ __device__ __forceinline__ void act1d_nlc_segment(const TIn* __restrict__ xb, TO
 #pragma unroll
             for (int s = 0; s < 7; ++s) nxt2[s] = ldx(g0 + 20 + s);
         }
-        act1d_nlc_body<TOut, PRECISE, EDGE, false>(xw, ve, vo, cur, vlast, coef, e, g0, yrel, C);
+        act1d_nlc_body<TOut, PRECISE, EDGE, false>(xw, acc, cur, vlast, coef, e, g0, yrel, C);
     }
 }
 
@@ -353,7 +369,7 @@ act1d_nlc_tma_kernel(const __grid_constant__ CUtensorMap map_x, TOut* __restrict
         e.n_out = static_cast<int>(min(static_cast<int64_t>(L), T - t0));
         e.first_seg = (t0 == 0);
 
-        float2 xw[7], ve[7], vo[7], cur[7], nxt[7];
+        float2 xw[7], acc[7], cur[7], nxt[7];
         float2 vlast = splat(0.f), xlast = splat(0.f);
         // slab 0: rows t0-7 .. t0-1; the window starts with rows t0-6 .. t0-1
         mbar_wait(&full[st], ph);
@@ -366,7 +382,7 @@ act1d_nlc_tma_kernel(const __grid_constant__ CUtensorMap map_x, TOut* __restrict
         if (lane == 0) mbar_arrive(&empty[st]);
         if (++st == p.stages) { st = 0; ph ^= 1; }
 #pragma unroll
-        for (int s = 0; s < 7; ++s) ve[s] = vo[s] = splat(0.f);
+        for (int s = 0; s < 7; ++s) acc[s] = splat(0.f);
         // the slab of body b+1 is read into registers before body b is computed, so its mbarrier wait and shared-memory
         // latency sit under ~350 instructions of FFMA2 / MUFU work
         auto fetch = [&](float2 (&dst)[7]) {
@@ -398,15 +414,15 @@ act1d_nlc_tma_kernel(const __grid_constant__ CUtensorMap map_x, TOut* __restrict
 #pragma unroll
                         for (int j = 0; j < 6; ++j) xw[j] = cur[0];
                     }
-                    act1d_nlc_body<TOut, PRECISE, true, true>(xw, ve, vo, cur, vlast, coef, e, 0, yrel, C);
+                    act1d_nlc_body<TOut, PRECISE, true, true>(xw, acc, cur, vlast, coef, e, 0, yrel, C);
                 } else {
-                    act1d_nlc_body<TOut, PRECISE, true, false>(xw, ve, vo, cur, vlast, coef, e, g0, yrel, C);
+                    act1d_nlc_body<TOut, PRECISE, true, false>(xw, acc, cur, vlast, coef, e, g0, yrel, C);
                 }
             } else {
                 if (body == 0)
-                    act1d_nlc_body<TOut, PRECISE, false, true>(xw, ve, vo, cur, vlast, coef, e, 0, yrel, C);
+                    act1d_nlc_body<TOut, PRECISE, false, true>(xw, acc, cur, vlast, coef, e, 0, yrel, C);
                 else
-                    act1d_nlc_body<TOut, PRECISE, false, false>(xw, ve, vo, cur, vlast, coef, e, g0, yrel, C);
+                    act1d_nlc_body<TOut, PRECISE, false, false>(xw, acc, cur, vlast, coef, e, g0, yrel, C);
             }
         }
     }
