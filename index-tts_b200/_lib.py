@@ -10,6 +10,8 @@ import threading
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libbvg.so")
+if os.environ.get("BVG_LIB_PATH"):  # developer A/B of kernel build variants (tools/build_variant.sh)
+    LIB_PATH = os.environ["BVG_LIB_PATH"]
 
 BVG_F32, BVG_BF16 = 0, 1
 BVG_EXACT_F32, BVG_BF16_TC = 0, 1

@@ -108,8 +108,8 @@ struct ActEdge {
 // in registers instead of a 14-entry history of the activated signal.  acc[(s+j+3)%7] holds y[m+j] at step s.
 template <typename TOut, bool PRECISE, bool EDGE, bool FIRST>
 __device__ __forceinline__ void act1d_nlc_body(float2 (&xw)[7], float2 (&acc)[7], const float2 (&cur)[7], float2& vlast,
-                                               const SnakeCoef& coef, const ActEdge& e, int g0, TOut* __restrict__ yrel,
-                                               int64_t C) {
+                                               const SnakeCoef& coef, const ActEdge& e, int g0, uint8_t*& yp,
+                                               int64_t row_bytes) {
     const float2 E0 = splat(2.f * BVG_F0), E1 = splat(2.f * BVG_F1), E2 = splat(2.f * BVG_F2),
                  E3 = splat(2.f * BVG_F3), E4 = splat(2.f * BVG_F4), E5 = splat(2.f * BVG_F5);
     const float2 G0 = splat(BVG_F0), G1 = splat(BVG_F1), G2 = splat(BVG_F2), G3 = splat(BVG_F3), G4 = splat(BVG_F4),
@@ -175,8 +175,9 @@ __device__ __forceinline__ void act1d_nlc_body(float2 (&xw)[7], float2 (&acc)[7]
         ym2 = ffma2(G1, o, ym2);
         if (!FIRST || s == 6) {
             const int i = g - 6;  // output row relative to t0
-            if (!EDGE || i < e.n_out) PairIO<TOut>::store(yrel + (int64_t)i * C, ym3);
+            if (!EDGE || i < e.n_out) PairIO<TOut>::store(reinterpret_cast<TOut*>(yp), ym3);
         }
+        yp += row_bytes;  // running byte pointer (row g - 6 of the segment): one 64-bit add per row, no multiply per store
     }
 }
 
@@ -213,7 +214,9 @@ __device__ __forceinline__ void act1d_nlc_segment(const TIn* __restrict__ xb, TO
     for (int s = 0; s < 7; ++s) nxt[s] = nbody > 1 ? ldx(13 + s) : splat(0.f);
 #pragma unroll
     for (int s = 0; s < 7; ++s) nxt2[s] = nbody > 2 ? ldx(20 + s) : splat(0.f);
-    act1d_nlc_body<TOut, PRECISE, EDGE, true>(xw, acc, cur, vlast, coef, e, 0, yrel, C);
+    const int64_t row_bytes = (int64_t)C * (int64_t)sizeof(TOut);
+    uint8_t* yp = reinterpret_cast<uint8_t*>(yrel) - 6 * row_bytes;  // row -6: never dereferenced before row 0
+    act1d_nlc_body<TOut, PRECISE, EDGE, true>(xw, acc, cur, vlast, coef, e, 0, yp, row_bytes);
 #pragma unroll 1
     for (int body = 1; body < nbody; ++body) {
         const int g0 = 7 * body;
@@ -223,7 +226,7 @@ __device__ __forceinline__ void act1d_nlc_segment(const TIn* __restrict__ xb, TO
 #pragma unroll
             for (int s = 0; s < 7; ++s) nxt2[s] = ldx(g0 + 20 + s);
         }
-        act1d_nlc_body<TOut, PRECISE, EDGE, false>(xw, acc, cur, vlast, coef, e, g0, yrel, C);
+        act1d_nlc_body<TOut, PRECISE, EDGE, false>(xw, acc, cur, vlast, coef, e, g0, yp, row_bytes);
     }
 }
 
@@ -262,6 +265,12 @@ act1d_nlc_kernel(const TIn* __restrict__ x, TOut* __restrict__ y, const float* _
 constexpr int ACT_TMA_COMPUTE = 256;
 constexpr int ACT_TMA_THREADS = ACT_TMA_COMPUTE + 32;
 constexpr int ACT_TMA_MAX_STAGES = 8;
+#ifndef ACT_TMA_MIN_CTAS
+#define ACT_TMA_MIN_CTAS 2
+#endif
+#ifndef ACT_TMA_PREFETCH
+#define ACT_TMA_PREFETCH 0  // register prefetch of the next slab: measured neutral (gpurun r01s), costs 14 MOV per body
+#endif
 
 struct ActTmaParams {
     int64_t T;
@@ -296,7 +305,7 @@ struct SmemPair<__nv_bfloat16> {
 };
 
 template <typename TIn, typename TOut, bool PRECISE>
-__global__ void __launch_bounds__(ACT_TMA_THREADS, 2)
+__global__ void __launch_bounds__(ACT_TMA_THREADS, ACT_TMA_MIN_CTAS)
 act1d_nlc_tma_kernel(const __grid_constant__ CUtensorMap map_x, TOut* __restrict__ y, const float* __restrict__ alpha,
                      const float* __restrict__ beta, const __grid_constant__ ActTmaParams p) {
     extern __shared__ uint8_t act_smem_raw[];
@@ -362,6 +371,8 @@ act1d_nlc_tma_kernel(const __grid_constant__ CUtensorMap map_x, TOut* __restrict
         const int ch = static_cast<int>(cch) * p.CC + 2 * pair;
         const SnakeCoef coef = make_coef<PRECISE>(alpha[ch], alpha[ch + 1], beta[ch], beta[ch + 1]);
         TOut* yrel = y + (static_cast<int64_t>(b) * T + t0) * C + ch;
+        const int64_t row_bytes = static_cast<int64_t>(C) * static_cast<int64_t>(sizeof(TOut));
+        uint8_t* yp = reinterpret_cast<uint8_t*>(yrel) - 6 * row_bytes;  // row -6: never dereferenced before row 0
 
         ActEdge e;
         e.rel_lo = e.rel_hi = 0;
@@ -369,7 +380,10 @@ act1d_nlc_tma_kernel(const __grid_constant__ CUtensorMap map_x, TOut* __restrict
         e.n_out = static_cast<int>(min(static_cast<int64_t>(L), T - t0));
         e.first_seg = (t0 == 0);
 
-        float2 xw[7], acc[7], cur[7], nxt[7];
+        float2 xw[7], acc[7], cur[7];
+#if ACT_TMA_PREFETCH
+        float2 nxt[7];
+#endif
         float2 vlast = splat(0.f), xlast = splat(0.f);
         // slab 0: rows t0-7 .. t0-1; the window starts with rows t0-6 .. t0-1
         mbar_wait(&full[st], ph);
@@ -394,13 +408,19 @@ act1d_nlc_tma_kernel(const __grid_constant__ CUtensorMap map_x, TOut* __restrict
             if (lane == 0) mbar_arrive(&empty[st]);
             if (++st == p.stages) { st = 0; ph ^= 1; }
         };
+#if ACT_TMA_PREFETCH
         fetch(nxt);
+#endif
 
 #pragma unroll 1
         for (int body = 0; body < p.nbody; ++body) {
+#if ACT_TMA_PREFETCH
 #pragma unroll
             for (int s = 0; s < 7; ++s) cur[s] = nxt[s];
             if (body + 1 < p.nbody) fetch(nxt);
+#else
+            fetch(cur);
+#endif
             if (!active) continue;
             const int g0 = 7 * body;
             if (edge_path) {
@@ -414,15 +434,15 @@ act1d_nlc_tma_kernel(const __grid_constant__ CUtensorMap map_x, TOut* __restrict
 #pragma unroll
                         for (int j = 0; j < 6; ++j) xw[j] = cur[0];
                     }
-                    act1d_nlc_body<TOut, PRECISE, true, true>(xw, acc, cur, vlast, coef, e, 0, yrel, C);
+                    act1d_nlc_body<TOut, PRECISE, true, true>(xw, acc, cur, vlast, coef, e, 0, yp, row_bytes);
                 } else {
-                    act1d_nlc_body<TOut, PRECISE, true, false>(xw, acc, cur, vlast, coef, e, g0, yrel, C);
+                    act1d_nlc_body<TOut, PRECISE, true, false>(xw, acc, cur, vlast, coef, e, g0, yp, row_bytes);
                 }
             } else {
                 if (body == 0)
-                    act1d_nlc_body<TOut, PRECISE, false, true>(xw, acc, cur, vlast, coef, e, 0, yrel, C);
+                    act1d_nlc_body<TOut, PRECISE, false, true>(xw, acc, cur, vlast, coef, e, 0, yp, row_bytes);
                 else
-                    act1d_nlc_body<TOut, PRECISE, false, false>(xw, acc, cur, vlast, coef, e, g0, yrel, C);
+                    act1d_nlc_body<TOut, PRECISE, false, false>(xw, acc, cur, vlast, coef, e, g0, yp, row_bytes);
             }
         }
     }
@@ -723,7 +743,7 @@ static int launch_nlc_tma(const void* x, void* y, const float* alpha, const floa
     // same L1/shared split as the conv kernel: CTAs of the two kernels can then be resident on one SM at the same time
     BVG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     static const int grid_mode = []() { const char* e = getenv("BVG_ACT_GRID"); return e ? atoi(e) : 0; }();
-    int grid = static_cast<int>(units < 2ll * sms ? units : 2ll * sms);
+    int grid = static_cast<int>(units < (long long)ACT_TMA_MIN_CTAS * sms ? units : (long long)ACT_TMA_MIN_CTAS * sms);
     if (grid_mode == 1) grid = static_cast<int>(units);                      // one unit per CTA: hardware load balancing
     if (grid_mode == 2) grid = static_cast<int>(units < sms ? units : sms);  // one CTA per SM
     kern<<<grid, ACT_TMA_THREADS, smem_bytes, st>>>(map, static_cast<TOut*>(y), alpha, beta, p);
