@@ -313,6 +313,7 @@ act1d_nlc_tma_kernel(const __grid_constant__ CUtensorMap map_x, TOut* __restrict
     uint64_t* full = reinterpret_cast<uint64_t*>(smem + p.stages * p.stage_bytes);
     uint64_t* empty = full + ACT_TMA_MAX_STAGES;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    griddep_launch_dependents();  // PDL: see sm100_ptx.cuh; only the producer warp touches produced data before its wait
     if (threadIdx.x == 0) {
         tma_prefetch_desc(&map_x);
         for (int i = 0; i < p.stages; ++i) {
@@ -329,6 +330,7 @@ act1d_nlc_tma_kernel(const __grid_constant__ CUtensorMap map_x, TOut* __restrict
 
     if (warp == ACT_TMA_COMPUTE / 32) {
         // ------------------------------ TMA producer ------------------------------
+        griddep_wait();  // x is produced by the previous kernel of the stream
         for (uint32_t unit = blockIdx.x; unit < p.n_units; unit += gridDim.x) {
             const uint32_t cch = unit % p.n_cchunks;
             const uint32_t rest = unit / p.n_cchunks;
@@ -746,7 +748,19 @@ static int launch_nlc_tma(const void* x, void* y, const float* alpha, const floa
     int grid = static_cast<int>(units < (long long)ACT_TMA_MIN_CTAS * sms ? units : (long long)ACT_TMA_MIN_CTAS * sms);
     if (grid_mode == 1) grid = static_cast<int>(units);                      // one unit per CTA: hardware load balancing
     if (grid_mode == 2) grid = static_cast<int>(units < sms ? units : sms);  // one CTA per SM
-    kern<<<grid, ACT_TMA_THREADS, smem_bytes, st>>>(map, static_cast<TOut*>(y), alpha, beta, p);
+    {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(grid);
+        cfg.blockDim = dim3(ACT_TMA_THREADS);
+        cfg.dynamicSmemBytes = smem_bytes;
+        cfg.stream = st;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = pdl_enabled() ? 1 : 0;
+        BVG_CUDA(cudaLaunchKernelEx(&cfg, kern, map, static_cast<TOut*>(y), alpha, beta, p));
+    }
     BVG_LAUNCH_CHECK("act1d_nlc_tma_kernel");
     return BVG_OK;
 }

@@ -261,6 +261,10 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns));
         p.trace[13 * static_cast<size_t>(p.trace_n) + blockIdx.x] = ns;  // CTA start (ns)
     }
+    // PDL: the next kernel of the stream may become resident as soon as this CTA's resources free up; everything this
+    // kernel does before griddep_wait() below (barrier init, TMEM allocation, bias copy, stationary weight loads) only
+    // touches constants, so it overlaps the tail of the previous kernel.
+    griddep_launch_dependents();
     if (threadIdx.x == 0) {
         tma_prefetch_desc(&map_x);
         tma_prefetch_desc(&map_w);
@@ -303,6 +307,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                                              kb * UMMA_BLOCK_K, n0, j, kPolicyEvictLast);
             }
         }
+        griddep_wait();  // activations are produced by the previous kernels of the stream
         // per-group cursors into the groups' A sub-rings (tiles alternate between the groups)
         const int a_per = p.a_stages / p.ng;
         int sa = 0, sa_other = 0, sb = 0, g = 0;
@@ -358,6 +363,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
     } else if (warp == 6) {
         // ------------------------------ residual / accum chunk loader ------------------------------
         if (n_ld > 0) {
+            griddep_wait();  // residual / running-sum tensors are produced by previous kernels
             // like the A ring, the chunk ring is split into one sub-ring per pipeline group: a slot is then always
             // refilled for the same consumer warps, which keeps the parity protocol unambiguous
             const int ld_per = p.ld_stages / p.ng;
@@ -743,7 +749,19 @@ int conv_umma_launch(const void* x, const void* w_packed, const float* bias, con
     if (p.has_acc && (rc = encode_io_4d(&map_acc, accum, false, cout_phase, num_phases, T, B, 128, "accum")) != BVG_OK) return rc;
     if (p.has_y32 && (rc = encode_io_4d(&map_y32, y_f32, false, cout_phase, num_phases, T, B, 32, "y_f32")) != BVG_OK) return rc;
     if (p.has_y16 && (rc = encode_io_4d(&map_y16, y_bf16, true, cout_phase, num_phases, T, B, 32, "y_bf16")) != BVG_OK) return rc;
-    conv_umma_kernel<<<grid, p.ng == 2 ? UMMA_THREADS2 : UMMA_THREADS, smem_bytes, st>>>(map_x, map_w, map_res, map_acc, map_y32, map_y16, p);
+    {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(grid);
+        cfg.blockDim = dim3(p.ng == 2 ? UMMA_THREADS2 : UMMA_THREADS);
+        cfg.dynamicSmemBytes = smem_bytes;
+        cfg.stream = st;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = pdl_enabled() ? 1 : 0;
+        BVG_CUDA(cudaLaunchKernelEx(&cfg, conv_umma_kernel, map_x, map_w, map_res, map_acc, map_y32, map_y16, p));
+    }
     BVG_LAUNCH_CHECK("conv_umma_kernel");
     return BVG_OK;
 }

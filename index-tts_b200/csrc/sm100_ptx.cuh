@@ -222,4 +222,13 @@ __host__ __device__ constexpr uint32_t umma_idesc_bf16_f32(uint32_t M, uint32_t 
            | ((M >> 4) << 24);  // M, 4 LSBs dropped
 }
 
+
+// Programmatic dependent launch (PDL): a kernel launched with cudaLaunchAttributeProgrammaticStreamSerialization may
+// become resident while its predecessor in the stream is still draining.  griddep_launch_dependents() lets the
+// successor start (its prologue and constant loads then overlap this kernel); griddep_wait() blocks until the
+// predecessor grid has completed and its writes are visible -- it must precede every access to data that earlier
+// kernels produce or still read.
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void griddep_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 }  // namespace bvg

@@ -1,5 +1,6 @@
 // Host-side cuTensorMapEncodeTiled access without linking libcuda: the entry point is fetched through the runtime.
 #pragma once
+#include <cstdlib>
 #include <cuda.h>
 #include <cuda_runtime.h>
 
@@ -17,6 +18,15 @@ static inline EncodeTiledFn get_encode_fn() {
         return reinterpret_cast<EncodeTiledFn>(f);
     }();
     return fn;
+}
+
+// Programmatic dependent launch for the persistent kernels of the forward plan (BVG_PDL=0 switches it off for A/B runs).
+static inline bool pdl_enabled() {
+    static const bool v = []() {
+        const char* e = getenv("BVG_PDL");
+        return !(e != nullptr && e[0] == '0');
+    }();
+    return v;
 }
 
 static inline int device_sm_count() {
