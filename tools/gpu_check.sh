@@ -26,3 +26,14 @@ if [ "${SKIP_NCU:-0}" != "1" ]; then
   echo "ncu act rc=$?"
 fi
 ls -la "${OUT}"
+if [ "${SKIP_NCU:-0}" != "1" ]; then
+  C3="python tools/run_one.py act 24 220672 bf16"
+  timeout 120 $C3 > "${OUT}/plain_act24.log" 2>&1 &&
+  timeout 600 ncu --set full --clock-control none --import-source on -k regex:act1d -s 2 -c 1 -f -o "${OUT}/prof_act_c24_bf16" $C3 > "${OUT}/ncu_act24.log" 2>&1
+  echo "ncu act24 rc=$?"
+  C4="python tools/run_one.py conv 24 220672 11 1 1"
+  timeout 120 $C4 > "${OUT}/plain_conv24.log" 2>&1 &&
+  timeout 600 ncu --set full --clock-control none --import-source on -k regex:conv_umma -s 2 -c 1 -f -o "${OUT}/prof_conv_c24k11res" $C4 > "${OUT}/ncu_conv24.log" 2>&1
+  echo "ncu conv24 rc=$?"
+fi
+ls -la "${OUT}"
