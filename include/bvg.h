@@ -141,6 +141,13 @@ typedef struct {
     const void* w;     /* packed weight (bvg_pack_*), dtype per precision */
     const float* bias; /* [Cout] or NULL */
     int32_t cin, cout, k, dilation;
+    /* Time folding (AMP-block convs of small-channel stages, BVG_BF16_TC only; 0 or 1 = off).  A [B, T, C] tensor is
+     * bit-identical in memory to [B, T/fold, fold*C], and a C -> C conv with k taps and dilation d over the first view
+     * equals a (fold*C) -> (fold*C) conv with 2*ceil((k-1)*d/2 / fold) + 1 taps and dilation 1 over the second one, with a
+     * block-structured weight.  When fold > 1, `w` holds that folded weight packed like any Conv1d
+     * ([taps'][fold*Cout][fold*Cin]) and `bias` the bias repeated fold times; cin / cout / k / dilation keep describing
+     * the reference layer.  It turns 48-byte rows and N = 24 MMAs into 192-byte rows and N = 96 MMAs with 4x fewer tiles. */
+    int32_t fold, reserved;
 } bvg_conv_desc;
 
 typedef struct {

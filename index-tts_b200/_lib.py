@@ -22,7 +22,7 @@ c_i64, c_int, c_f32, c_vp, c_sz = C.c_int64, C.c_int, C.c_float, C.c_void_p, C.c
 
 class ConvDesc(C.Structure):
     _fields_ = [("w", c_vp), ("bias", c_vp), ("cin", C.c_int32), ("cout", C.c_int32), ("k", C.c_int32),
-                ("dilation", C.c_int32)]
+                ("dilation", C.c_int32), ("fold", C.c_int32), ("reserved", C.c_int32)]
 
 
 class ActDesc(C.Structure):

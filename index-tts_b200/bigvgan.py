@@ -234,6 +234,34 @@ _PLANS: "weakref.WeakValueDictionary[int, _PackedGenerator]" = weakref.WeakValue
 _next_plan_id = [1]
 
 
+def fold_conv1d_weight(w: torch.Tensor, dilation: int, fold: int) -> torch.Tensor:
+    """Time-folded form of a 'same'-padded Conv1d weight (include/bvg.h, ``bvg_conv_desc::fold``).
+
+    ``w`` is ``[Cout, Cin, k]`` (k odd).  Viewing ``[B, T, C]`` as ``[B, T/fold, fold*C]``, output phase ``po`` of folded
+    row ``t'`` is original row ``fold*t' + po``; tap ``j`` reads original row ``fold*t' + po + (j - (k-1)/2)*dilation``,
+    i.e. folded row ``t' + floor(q / fold)`` phase ``q mod fold`` with ``q = po + (j - (k-1)/2)*dilation``.  Returns
+    ``[fold*Cout, fold*Cin, taps']`` with ``taps' = 2*ceil(((k-1)/2*dilation) / fold) + 1`` for a dilation-1 conv."""
+    cout, cin, k = w.shape
+    reach = (k - 1) // 2 * dilation
+    pad = -(-reach // fold)
+    taps = 2 * pad + 1
+    out = torch.zeros(fold * cout, fold * cin, taps, dtype=w.dtype, device=w.device)
+    for po in range(fold):
+        for j in range(k):
+            q = po + (j - (k - 1) // 2) * dilation
+            tt, pi = q // fold, q % fold  # Python floor division / non-negative modulo
+            out[po * cout:(po + 1) * cout, pi * cin:(pi + 1) * cin, tt + pad] = w[:, :, j]
+    return out
+
+
+# Fold AMP-block convs of stages with at most this many channels by FOLD_FACTOR when the folded conv needs at most
+# FOLD_MAX_TAPS taps (the folded GEMM does fold*taps'/k times the FLOPs on an otherwise idle tensor pipe; beyond ~5 taps
+# the weights stop being shared-memory resident and the layer gets slower instead).  BVG_FOLD=0 switches it off.
+FOLD_MAX_CHANNELS = 32
+FOLD_FACTOR = 4
+FOLD_MAX_TAPS = 5
+
+
 class _PackedGenerator:
     """Folded + packed weights of one BigVGAN on one device in one precision, and the C descriptor pointing at them."""
 
@@ -267,14 +295,29 @@ class _PackedGenerator:
             self.keep.append(t)
             return t
 
-        def conv(dst, m, transposed=False):
+        fold_ok = precision == _lib.BVG_BF16_TC and os.environ.get("BVG_FOLD", "1") != "0"
+
+        def conv(dst, m, transposed=False, time_factor=0):
+            dst.cin, dst.cout = int(m.in_channels), int(m.out_channels)
+            dst.k = int(m.kernel_size[0])
+            dst.dilation = int(m.dilation[0])
+            dst.fold = 0
+            r = FOLD_FACTOR
+            if (fold_ok and not transposed and time_factor % r == 0 and dst.cin == dst.cout
+                    and dst.cin <= FOLD_MAX_CHANNELS and dst.k % 2 == 1
+                    and 2 * -(-((dst.k - 1) // 2 * dst.dilation) // r) + 1 <= FOLD_MAX_TAPS):
+                wf = fold_conv1d_weight(_effective_weight(m).detach().to(device=device, dtype=torch.float32),
+                                        dst.dilation, r)
+                w = ops.pack_conv1d_weight(wf, precision)
+                self.keep.append(w)
+                dst.w = w.data_ptr()
+                dst.bias = f32(m.bias.detach().repeat(r)).data_ptr() if m.bias is not None else None
+                dst.fold = r
+                return
             w = m.packed(precision)
             self.keep.append(w)
             dst.w = w.data_ptr()
             dst.bias = f32(m.bias).data_ptr() if m.bias is not None else None
-            dst.cin, dst.cout = int(m.in_channels), int(m.out_channels)
-            dst.k = int(m.kernel_size[0])
-            dst.dilation = int(m.dilation[0])
 
         def act(dst, a):
             al, be = a.log_params()
@@ -282,18 +325,20 @@ class _PackedGenerator:
             dst.beta_log = f32(be).data_ptr()
 
         conv(d.conv_pre, model.conv_pre)
+        time_factor = 1  # T of the stage = time_factor * T_mel: folding by r needs r | time_factor
         for i in range(model.num_upsamples):
             if len(model.ups[i]) != 1:
                 raise NotImplementedError("one transposed conv per upsample stage expected")
             conv(d.ups[i], model.ups[i][0], transposed=True)
+            time_factor *= int(h.upsample_rates[i])
             for j in range(model.num_kernels):
                 rb = model.resblocks[i * model.num_kernels + j]
                 if not isinstance(rb, AMPBlock1):
                     raise NotImplementedError("the fused generator plan implements resblock '1' (AMPBlock1); "
                                               "AMPBlock2 is available as a standalone module only")
                 for l in range(d.num_dilations):
-                    conv(d.convs1[i][j][l], rb.convs1[l])
-                    conv(d.convs2[i][j][l], rb.convs2[l])
+                    conv(d.convs1[i][j][l], rb.convs1[l], time_factor=time_factor)
+                    conv(d.convs2[i][j][l], rb.convs2[l], time_factor=time_factor)
                 for a in range(2 * d.num_dilations):
                     act(d.acts[i][j][a], rb.activations[a])
         act(d.act_post, model.activation_post)

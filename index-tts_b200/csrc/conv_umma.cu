@@ -633,6 +633,20 @@ int conv_umma_launch(const void* x, const void* w_packed, const float* bias, con
         int nt = (cp + 255) / 256;
         // several tiles per phase: 32-column granularity so that epilogue chunks never straddle tiles
         int tile = (int)round_up(ceil_div(cp, nt), nt > 1 ? 32 : 16);
+        // Small problems (a single utterance, a time shard): with the widest tile the grid would leave most SMs idle,
+        // so narrow the N tile until the tiles fill the machine.  Cost model: waves x max(tile, 96) -- below ~96
+        // columns a tile stops getting cheaper (the A operand reads and the UMMA issue rate dominate).
+        const int64_t mt_all = ceil_div(T, UMMA_BLOCK_M) * B * num_phases;
+        const int sms_l = device_sm_count();
+        if (mt_all * ceil_div(cp, tile) < sms_l && cp >= 64) {
+            int64_t best_cost = ceil_div(mt_all * ceil_div(cp, tile), sms_l) * (tile > 96 ? tile : 96);
+            for (int nt_c = nt + 1; nt_c <= cp / 32; ++nt_c) {
+                const int tile_c = (int)round_up(ceil_div(cp, nt_c), 32);
+                const int64_t tiles_c = mt_all * ceil_div(cp, tile_c);
+                const int64_t cost = ceil_div(tiles_c, sms_l) * (tile_c > 96 ? tile_c : 96);
+                if (cost < best_cost) { best_cost = cost; tile = tile_c; }
+            }
+        }
         p.n_tile = tile;
         p.tiles_per_phase = (int)ceil_div(cp, tile);
     }

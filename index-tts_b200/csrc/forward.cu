@@ -38,6 +38,18 @@ static int conv1d(int precision, const void* x, const void* w, const float* bias
                          out_scale, st);
 }
 
+// AMP-block conv through its descriptor: plain, or time-folded (bvg.h, bvg_conv_desc::fold) in tensor-core mode.
+static int conv1d_desc(int precision, const bvg_conv_desc& c, const void* x, const float* residual, const float* accum,
+                       float* y_f32, void* y_bf16, int64_t B, int64_t T, int64_t C, float out_scale, cudaStream_t st) {
+    const int r = c.fold;
+    if (r <= 1 || precision != BVG_BF16_TC)
+        return conv1d(precision, x, c.w, c.bias, residual, accum, y_f32, y_bf16, B, T, C, C, c.k, c.dilation, out_scale, st);
+    BVG_REQUIRE(T % r == 0, BVG_ERR_INVALID, "conv1d: time folding by %d needs T %% %d == 0 (T = %lld)", r, r, (long long)T);
+    const int reach = (c.k - 1) / 2 * c.dilation;
+    const int taps = 2 * ((reach + r - 1) / r) + 1;
+    return conv1d(precision, x, c.w, c.bias, residual, accum, y_f32, y_bf16, B, T / r, C * r, C * r, taps, 1, out_scale, st);
+}
+
 static int convtranspose1d(int precision, const void* x, const void* w, const float* bias, float* y_f32, void* y_bf16,
                            int64_t B, int64_t Tin, int64_t Cin, int64_t Cout, int K, int u, cudaStream_t st) {
     BVG_REQUIRE(u >= 1 && u <= BVG_MAX_PHASES && K % u == 0 && (K - u) % 2 == 0, BVG_ERR_UNSUPPORTED,
@@ -277,8 +289,8 @@ extern "C" int bvg_forward(const bvg_model_desc* m, const float* mel, int64_t me
                 {
                     ProfScope ps(BVG_K_CONV1D, i, C, C, c1.k, c1.dilation, B * T, conv_flops(C, C, c1.k, rows),
                                  conv_bytes(C, C, c1.k, rows, false), sj);
-                    rc = conv1d(prec, A, c1.w, c1.bias, nullptr, nullptr, tc ? nullptr : reinterpret_cast<float*>(Y1),
-                                tc ? Y1 : nullptr, B, T, C, C, c1.k, c1.dilation, 1.0f, sj);
+                    rc = conv1d_desc(prec, c1, A, nullptr, nullptr, tc ? nullptr : reinterpret_cast<float*>(Y1),
+                                     tc ? Y1 : nullptr, B, T, C, 1.0f, sj);
                 }
                 if (rc != BVG_OK) return rc;
                 {
@@ -291,7 +303,7 @@ extern "C" int bvg_forward(const bvg_model_desc* m, const float* mel, int64_t me
                 const bool last = (l + 1 == m->num_dilations);
                 if (!last) {
                     // x = xt + x
-                    rc = conv1d(prec, A, c2.w, c2.bias, xr, nullptr, R, nullptr, B, T, C, C, c2.k, 1, 1.0f, sj);
+                    rc = conv1d_desc(prec, c2, A, xr, nullptr, R, nullptr, B, T, C, 1.0f, sj);
                     xr = R;
                 } else {
                     // xs (+)= block output; x = xs / num_kernels (bigvgan.py:369-375) folded into the epilogue: the
@@ -299,8 +311,8 @@ extern "C" int bvg_forward(const bvg_model_desc* m, const float* mel, int64_t me
                     // stage also emits the operand-dtype copy the next transposed conv reads.
                     if (aux && j > 0) BVG_CUDA(cudaStreamWaitEvent(sj, aux->last[j - 1], 0));
                     const bool emit_op = tc && !last_stage && (j + 1 == m->num_kernels);
-                    rc = conv1d(prec, A, c2.w, c2.bias, xr, j > 0 ? SUM : nullptr, SUM, emit_op ? SUMOP : nullptr, B, T, C, C,
-                                c2.k, 1, inv_nk, sj);
+                    rc = conv1d_desc(prec, c2, A, xr, j > 0 ? SUM : nullptr, SUM, emit_op ? SUMOP : nullptr, B, T, C, inv_nk,
+                                     sj);
                     if (aux && rc == BVG_OK) BVG_CUDA(cudaEventRecord(aux->last[j], sj));
                 }
                 if (rc != BVG_OK) return rc;
