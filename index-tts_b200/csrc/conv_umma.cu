@@ -175,10 +175,10 @@ __device__ __forceinline__ void umma_issue_loop(const ConvUmmaParams& p, uint32_
     sA_d += static_cast<uint32_t>(group * a_stages) * a_stage_d;
     int sa = 0, sb = 0;
     uint32_t acc = 0, pa = 0, pb = 0, pacc = 0;
-    if (STAT) mbar_wait(&b_full[0], 0);
+    if (STAT) mbar_wait_warp(&b_full[0], 0);
     uint32_t it = 0;
     for (uint32_t tile = blockIdx.x + group * gridDim.x; tile < total; tile += ng * gridDim.x, ++it) {
-        mbar_wait(&acc_empty[acc], pacc ^ 1);
+        mbar_wait_warp(&acc_empty[acc], pacc ^ 1);
         tc_fence_after_sync();
         if (leader) trace_ev(p, 1 + 6 * group, it);
         const uint32_t d_tmem = tmem_base + (2 * group + acc) * n_tile;
@@ -188,7 +188,7 @@ __device__ __forceinline__ void umma_issue_loop(const ConvUmmaParams& p, uint32_
         for (int kb = 0; kb < k_blocks; ++kb) {
             const int k_steps = (kb + 1 == k_blocks) ? last_steps : 4;
             const bool k2 = k_steps > 1, k3 = k_steps > 2, k4 = k_steps > 3;
-            mbar_wait(&a_full[sa], pa);
+            mbar_wait_warp(&a_full[sa], pa);
             tc_fence_after_sync();
             if (leader && kb == 0) trace_ev(p, 2 + 6 * group, it);
             uint32_t a_d = sA_d + sa * a_stage_d;
@@ -199,7 +199,7 @@ __device__ __forceinline__ void umma_issue_loop(const ConvUmmaParams& p, uint32_
                     b_d = w_d;
                     w_d += b_step;
                 } else {
-                    mbar_wait(&b_full[sb], pb);
+                    mbar_wait_warp(&b_full[sb], pb);
                     tc_fence_after_sync();
                     b_d = sB_d + sb * b_step;
                 }
@@ -321,7 +321,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
             const int n0 = phase * p.cout_phase + (nt % p.tiles_per_phase) * p.n_tile;
             const int row0 = mt * UMMA_BLOCK_M + p.tap_base[phase];
             for (int kb = 0; kb < k_blocks; ++kb) {
-                mbar_wait(&a_empty[slot0 + sa], pa ^ 1);
+                mbar_wait_warp(&a_empty[slot0 + sa], pa ^ 1);
                 if (kb == 0 && lane == 0) trace_ev(p, 0, it);
                 if (elect_one()) {
                     if (p.dbg & 2) {
@@ -334,7 +334,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                 if (++sa == a_per) { sa = 0; pa ^= 1; }
                 if (!p.stationary) {
                     for (int j = 0; j < p.taps; ++j) {
-                        mbar_wait(&b_empty[sb], pb ^ 1);
+                        mbar_wait_warp(&b_empty[sb], pb ^ 1);
                         if (elect_one()) {
                             mbar_arrive_expect_tx(&b_full[sb], p.b_stage_bytes);
                             tma_load_3d_hint(sB + sb * p.b_stage_bytes, &map_w, &b_full[sb], kb * UMMA_BLOCK_K, n0, j,
@@ -378,7 +378,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                 const int slot0 = g * ld_per;
                 for (int c = 0; c < p.n_tile; c += EPI_CHUNK) {
                     const int slot = slot0 + s;
-                    mbar_wait(&ld_empty[slot], ps ^ 1);
+                    mbar_wait_warp(&ld_empty[slot], ps ^ 1);
                     if ((p.dbg & 4) && elect_one()) {
                         mbar_arrive(&ld_full[slot]);
                     } else if (elect_one()) {
@@ -425,7 +425,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
             const int phase = nt / p.tiles_per_phase;
             const int c0 = (nt % p.tiles_per_phase) * p.n_tile;  // channel offset inside the phase
 
-            mbar_wait(&acc_full[acc], pacc);
+            mbar_wait_warp(&acc_full[acc], pacc);
             tc_fence_after_sync();
             if (tracer) trace_ev(p, 4 + 6 * group, it);
             const uint32_t t_addr = tmem_base + ((static_cast<uint32_t>(q) * 32u) << 16) + (2 * group + acc) * p.n_tile;
@@ -472,7 +472,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                     }
                 }
                 if (n_ld > 0) {
-                    mbar_wait(&ld_full[ls], pls);
+                    mbar_wait_warp(&ld_full[ls], pls);
                     const uint8_t* ld = sLdG + ls * n_ld * EPI_LD_TILE_BYTES + row * 128;
                     if (p.has_res) {
 #pragma unroll

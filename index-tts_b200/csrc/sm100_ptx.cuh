@@ -70,6 +70,16 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     }
 }
 
+// Wait executed by a full, converged warp.  The loop condition is a warp vote, so the branch is warp-uniform BY
+// CONSTRUCTION: the compiler keeps the code after it convergent and the pipeline cursors (stage indices, shared-memory
+// descriptors) in uniform registers instead of moving them there with R2UR before every tcgen05.mma / TMA issue.
+__device__ __forceinline__ void mbar_wait_warp(uint64_t* bar, uint32_t parity) {
+    uint32_t spins = 0;
+    while (!__all_sync(0xffffffffu, mbar_try_wait(bar, parity))) {
+        if (++spins > 400000000u) __trap();  // protocol bug: trap instead of hanging the (shared) GPU
+    }
+}
+
 // ------------------------------------------------------------------------------------------------
 // TMA
 // ------------------------------------------------------------------------------------------------
