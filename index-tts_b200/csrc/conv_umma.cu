@@ -65,6 +65,11 @@ struct ConvUmmaParams {
     int64_t total_tiles;
     int a_stages, b_stages;
     uint32_t a_stage_bytes, b_stage_bytes;
+    // pair mode (mp = 2, weight-streaming layers): a tile is 256 rows = two 128-row sub-tiles that share every weight
+    // tile of the B ring (two accumulators per TMEM buffer), which halves the L2 -> shared-memory weight traffic; an A
+    // stage then holds two overlapping halo boxes 16 KB apart (a_box_bytes each)
+    int mp;
+    uint32_t a_box_bytes;
     uint32_t tmem_cols;
     // pipeline groups (1 or 2): group g owns the CTA's tiles i with i % ng == g, its own UMMA issuer warp, 4 epilogue
     // warps, 2 TMEM accumulators and output staging tiles; the TMA producer / loader warps feed both in tile order.
@@ -168,6 +173,7 @@ __device__ __forceinline__ void umma_issue_loop(const ConvUmmaParams& p, uint32_
     // each group consumes its own sub-ring of A stages (slots [group*a_stages, (group+1)*a_stages)), so a slot is
     // always refilled for the same consumer and the parity protocol stays unambiguous
     const int ng = p.ng;
+    const uint32_t mp = static_cast<uint32_t>(p.mp);
     acc_full += 2 * group;
     acc_empty += 2 * group;
     a_full += group * a_stages;
@@ -181,7 +187,7 @@ __device__ __forceinline__ void umma_issue_loop(const ConvUmmaParams& p, uint32_
         mbar_wait_warp(&acc_empty[acc], pacc ^ 1);
         tc_fence_after_sync();
         if (leader) trace_ev(p, 1 + 6 * group, it);
-        const uint32_t d_tmem = tmem_base + (2 * group + acc) * n_tile;
+        const uint32_t d_tmem = tmem_base + ((2 * group + acc) * mp) * n_tile;
         uint32_t accumulate = 0;
         uint32_t w_d = sB_d;  // stationary weight cursor
         if (STAT && n_tiles > 1) w_d += (tile % static_cast<uint32_t>(n_tiles)) * w_tile_d;
@@ -208,6 +214,13 @@ __device__ __forceinline__ void umma_issue_loop(const ConvUmmaParams& p, uint32_
                     if (k2) umma_f16_lo(d_tmem, a_d + 2, b_d + 2, desc_hi, idesc, 1);
                     if (k3) umma_f16_lo(d_tmem, a_d + 4, b_d + 4, desc_hi, idesc, 1);
                     if (k4) umma_f16_lo(d_tmem, a_d + 6, b_d + 6, desc_hi, idesc, 1);
+                    if (mp == 2) {  // second 128-row sub-tile: rows +128 (16 KB further), next accumulator, same weights
+                        const uint32_t a2 = a_d + 1024u, d2 = d_tmem + n_tile;
+                        umma_f16_lo(d2, a2, b_d, desc_hi, idesc, accumulate);
+                        if (k2) umma_f16_lo(d2, a2 + 2, b_d + 2, desc_hi, idesc, 1);
+                        if (k3) umma_f16_lo(d2, a2 + 4, b_d + 4, desc_hi, idesc, 1);
+                        if (k4) umma_f16_lo(d2, a2 + 6, b_d + 6, desc_hi, idesc, 1);
+                    }
                     if (!STAT) umma_commit(&b_empty[sb]);
                 }
                 accumulate = 1;
@@ -319,7 +332,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
             const int slot0 = g * a_per;
             const int phase = nt / p.tiles_per_phase;
             const int n0 = phase * p.cout_phase + (nt % p.tiles_per_phase) * p.n_tile;
-            const int row0 = mt * UMMA_BLOCK_M + p.tap_base[phase];
+            const int row0 = mt * UMMA_BLOCK_M * p.mp + p.tap_base[phase];
             for (int kb = 0; kb < k_blocks; ++kb) {
                 mbar_wait_warp(&a_empty[slot0 + sa], pa ^ 1);
                 if (kb == 0 && lane == 0) trace_ev(p, 0, it);
@@ -327,8 +340,13 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                     if (p.dbg & 2) {
                         mbar_arrive(&a_full[slot0 + sa]);
                     } else {
-                        mbar_arrive_expect_tx(&a_full[slot0 + sa], p.a_stage_bytes);
-                        tma_load_3d(sA + (slot0 + sa) * p.a_stage_bytes, &map_x, &a_full[slot0 + sa], kb * UMMA_BLOCK_K, row0, b);
+                        mbar_arrive_expect_tx(&a_full[slot0 + sa], p.mp * p.a_box_bytes);
+                        uint8_t* dst = sA + (slot0 + sa) * p.a_stage_bytes;
+                        tma_load_3d(dst, &map_x, &a_full[slot0 + sa], kb * UMMA_BLOCK_K, row0, b);
+                        // pair mode: the second halo box starts 128 rows (16 KB) further; the overlapping rows are
+                        // simply written twice with the same data
+                        if (p.mp == 2)
+                            tma_load_3d(dst + 16384, &map_x, &a_full[slot0 + sa], kb * UMMA_BLOCK_K, row0 + UMMA_BLOCK_M, b);
                     }
                 }
                 if (++sa == a_per) { sa = 0; pa ^= 1; }
@@ -372,11 +390,14 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
             TileWalker tw(blockIdx.x, gridDim.x, n_tiles, m_tiles);
             for (uint32_t tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, tw.next()) {
                 const TileCoord tc = tw.c;
-                const int nt = tc.nt, t0 = tc.mt * UMMA_BLOCK_M, b = tc.b;
+                const int nt = tc.nt, t00 = tc.mt * UMMA_BLOCK_M * p.mp, b = tc.b;
                 const int phase = nt / p.tiles_per_phase;
                 const int c0 = (nt % p.tiles_per_phase) * p.n_tile;
                 const int slot0 = g * ld_per;
-                for (int c = 0; c < p.n_tile; c += EPI_CHUNK) {
+                for (int sc = 0; sc < p.mp * p.n_tile; sc += EPI_CHUNK) {  // (sub-tile, chunk) in the epilogue's order
+                    const int sub = sc >= p.n_tile ? 1 : 0;
+                    const int c = sc - sub * p.n_tile;
+                    const int t0 = t00 + sub * UMMA_BLOCK_M;
                     const int slot = slot0 + s;
                     mbar_wait_warp(&ld_empty[slot], ps ^ 1);
                     if ((p.dbg & 4) && elect_one()) {
@@ -421,14 +442,17 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
         TileWalker tw(blockIdx.x + group * gridDim.x, p.ng * gridDim.x, n_tiles, m_tiles);
         for (uint32_t tile = blockIdx.x + group * gridDim.x; tile < total_tiles; tile += p.ng * gridDim.x, ++it, tw.next()) {
             const TileCoord tc = tw.c;
-            const int nt = tc.nt, t0 = tc.mt * UMMA_BLOCK_M, b = tc.b;
+            const int nt = tc.nt, t00 = tc.mt * UMMA_BLOCK_M * p.mp, b = tc.b;
             const int phase = nt / p.tiles_per_phase;
             const int c0 = (nt % p.tiles_per_phase) * p.n_tile;  // channel offset inside the phase
 
             mbar_wait_warp(&acc_full[acc], pacc);
             tc_fence_after_sync();
             if (tracer) trace_ev(p, 4 + 6 * group, it);
-            const uint32_t t_addr = tmem_base + ((static_cast<uint32_t>(q) * 32u) << 16) + (2 * group + acc) * p.n_tile;
+            for (int sub = 0; sub < p.mp; ++sub) {
+            const int t0 = t00 + sub * UMMA_BLOCK_M;
+            const uint32_t t_addr = tmem_base + ((static_cast<uint32_t>(q) * 32u) << 16) +
+                                    ((2 * group + acc) * p.mp + sub) * p.n_tile;
             for (int c = 0; c < p.n_tile; c += EPI_CHUNK) {
                 const int width = min(EPI_CHUNK, p.n_tile - c);  // 32 or 16
                 float o[32];
@@ -446,7 +470,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
 #pragma unroll
                     for (int e = 0; e < 32; ++e) o[e] = __uint_as_float(v[e]);
                 }
-                if (c + EPI_CHUNK >= p.n_tile) {  // last TMEM read of this tile: hand the accumulator back early
+                if (c + EPI_CHUNK >= p.n_tile && sub + 1 == p.mp) {  // last TMEM read of this tile: hand the accumulator back early
                     tc_fence_before_sync();
                     __syncwarp();
                     if (lane == 0) mbar_arrive(&acc_empty[acc]);
@@ -532,6 +556,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                 }
                 ob ^= 1;
             }
+            }  // sub
             if (++acc == 2) { acc = 0; pacc ^= 1; }
             if (tracer) trace_ev(p, 6 + 6 * group, it);
         }
@@ -647,15 +672,32 @@ int conv_umma_launch(const void* x, const void* w_packed, const float* bias, con
                 if (cost < best_cost) { best_cost = cost; tile = tile_c; }
             }
         }
+        // Pair mode for the weight-streaming mid-channel layers (C = 96, 192 with k >= 7): their B ring is bound by
+        // L2 -> shared-memory weight traffic (every 128-row tile re-reads all k * Cin * Cout weights), so two 128-row
+        // sub-tiles share each weight tile.  Needs four accumulators in TMEM (n_tile <= 128) and whole 32-column chunks.
+        p.mp = 1;
+        static const int pair_env = []() { const char* e = getenv("BVG_CONV_PAIR"); return e ? atoi(e) : 1; }();
+        const int kb_l = (int)ceil_div(Cin, UMMA_BLOCK_K);
+        if (pair_env && num_phases == 1 && Cin <= 192 && cp <= 128 &&
+            (int64_t)ceil_div(cp, tile) * kb_l * taps * round_up((int64_t)tile * 128, 1024) > 112 * 1024) {
+            // only where the N tile stays the whole layer: halving a 192-wide tile to fit four accumulators re-reads the
+            // activations and was measured slower (stage 2: 192 -> 210 us for k = 7), gpurun r01x
+            const int t2 = (cp <= 128 && cp % 32 == 0) ? cp : 0;
+            if (t2 > 0 && ceil_div(T, 2 * UMMA_BLOCK_M) * B * (cp / t2) >= 2 * (int64_t)sms_l) {
+                tile = t2;
+                p.mp = 2;
+            }
+        }
         p.n_tile = tile;
         p.tiles_per_phase = (int)ceil_div(cp, tile);
     }
-    p.m_tiles = ceil_div(T, UMMA_BLOCK_M);
+    p.m_tiles = ceil_div(T, UMMA_BLOCK_M * p.mp);
     p.total_tiles = p.m_tiles * B * p.num_phases * p.tiles_per_phase;
     BVG_REQUIRE(p.total_tiles < (int64_t(1) << 31) - 1024, BVG_ERR_UNSUPPORTED, "conv_umma: %lld tiles exceed the 32-bit tile index",
                 (long long)p.total_tiles);
     const int a_rows = (int)round_up(UMMA_BLOCK_M + (taps - 1) * dil, 8);
-    p.a_stage_bytes = (uint32_t)round_up((int64_t)a_rows * 128, 1024);
+    p.a_box_bytes = (uint32_t)round_up((int64_t)a_rows * 128, 1024);
+    p.a_stage_bytes = p.mp == 2 ? 16384u + p.a_box_bytes : p.a_box_bytes;
     p.b_stage_bytes = (uint32_t)round_up((int64_t)p.n_tile * 128, 1024);
     p.ng = 1;
     p.trace = g_conv_trace;
@@ -726,9 +768,11 @@ int conv_umma_launch(const void* x, const void* w_packed, const float* bias, con
     }
     BVG_REQUIRE(planned, BVG_ERR_UNSUPPORTED, "conv_umma: tile does not fit shared memory");
     BVG_REQUIRE(p.ng == 1 || p.stationary, BVG_ERR_UNSUPPORTED, "conv_umma: dual pipeline planned without stationary weights");
+    BVG_REQUIRE(p.mp == 1 || (!p.stationary && p.ng == 1 && 4 * p.n_tile <= 512 && p.n_tile % 32 == 0), BVG_ERR_UNSUPPORTED,
+                "conv_umma: pair mode planned for an unsuitable layer");
     {
         uint32_t tm = 32;
-        while (tm < (uint32_t)(2 * p.ng * p.n_tile)) tm <<= 1;
+        while (tm < (uint32_t)(2 * p.ng * p.mp * p.n_tile)) tm <<= 1;
         p.tmem_cols = tm;
     }
     const uint32_t smem_bytes = p.a_stages * p.a_stage_bytes + (p.stationary ? p.w_bytes : p.b_stages * p.b_stage_bytes) +
@@ -737,7 +781,7 @@ int conv_umma_launch(const void* x, const void* w_packed, const float* bias, con
 
     CUtensorMap map_x, map_w, map_res, map_acc, map_y32, map_y16;
     // the A box is a_stage_bytes/128 rows so that expect_tx matches the bytes TMA writes
-    const uint32_t a_box_rows = p.a_stage_bytes / 128;
+    const uint32_t a_box_rows = p.a_box_bytes / 128;
     BVG_REQUIRE(a_box_rows <= 256, BVG_ERR_UNSUPPORTED, "conv_umma: halo tile of %u rows exceeds the TMA box limit", a_box_rows);
     int rc = encode_3d_bf16(&map_x, x, (uint64_t)Cin, (uint64_t)T, (uint64_t)B, UMMA_BLOCK_K, a_box_rows, 1, "x");
     if (rc != BVG_OK) return rc;
