@@ -166,3 +166,69 @@ def test_submodule_forwards_match_fused_plan(golden_dir):
     from index_tts_b200 import ops
     post = ops.conv_post(ops.ncl_to_nlc(x, torch.float32), m.conv_post.weight, None, False)
     assert float((post - full).abs().max()) <= 2e-6
+
+
+def test_forward_on_side_stream_two_threads_and_graph_capture(full_models):
+    """SURVEY.md 8(b) threading / stream contract: launches go to the caller's current stream, two host threads may call
+    forward concurrently (serve_tars.py runs infer from a 2-worker ThreadPoolExecutor), and the plan (three-stream fork /
+    join, PDL launches) is CUDA-graph capturable.  All results must equal the plain call bit for bit."""
+    import threading
+    sd, m = full_models
+    m.set_precision("bf16")
+    mels = [torch.randn(1, 80, 40 + 7 * i, generator=torch.Generator().manual_seed(30 + i)).cuda() for i in range(4)]
+    with torch.no_grad():
+        want = [m(x).clone() for x in mels]
+    torch.cuda.synchronize()
+    # side stream
+    s = torch.cuda.Stream()
+    with torch.cuda.stream(s), torch.no_grad():
+        got = m(mels[0])
+    s.synchronize()
+    assert torch.equal(got, want[0])
+    # two threads, each on its own stream, interleaved calls
+    out, errs = {}, []
+
+    def worker(tid):
+        try:
+            st = torch.cuda.Stream()
+            with torch.cuda.stream(st), torch.no_grad():
+                for rep in range(3):
+                    for i in range(tid, 4, 2):
+                        out[(tid, rep, i)] = m(mels[i])
+            st.synchronize()
+        except Exception as e:  # pragma: no cover
+            errs.append(e)
+
+    ts = [threading.Thread(target=worker, args=(t,)) for t in range(2)]
+    [t.start() for t in ts]
+    [t.join() for t in ts]
+    assert not errs, errs
+    for (tid, rep, i), y in out.items():
+        assert torch.equal(y, want[i]), (tid, rep, i)
+    # CUDA graph capture + replay
+    static_in = mels[1].clone()
+    g = torch.cuda.CUDAGraph()
+    with torch.no_grad():
+        m(static_in)  # warm (workspace allocation, plan)
+        torch.cuda.synchronize()
+        with torch.cuda.graph(g):
+            static_out = m(static_in)
+    for i in (3, 1):
+        if mels[i].shape == static_in.shape:
+            static_in.copy_(mels[i])
+            g.replay()
+            torch.cuda.synchronize()
+            assert torch.equal(static_out, want[i])
+    m.set_precision("fp32")
+
+
+def test_torch_compile_dynamic(full_models):
+    """infer_v2.py:267-270 wraps the vocoder in torch.compile(dynamic=True): the custom op + fake kernel must trace."""
+    sd, m = full_models
+    m.set_precision("bf16")
+    cm = torch.compile(m, dynamic=True)
+    with torch.no_grad():
+        for T in (33, 47):
+            x = torch.randn(1, 80, T, generator=torch.Generator().manual_seed(T)).cuda()
+            assert torch.equal(cm(x), m(x))
+    m.set_precision("fp32")
