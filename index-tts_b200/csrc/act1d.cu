@@ -277,6 +277,7 @@ struct ActTmaParams {
     int C, CC, P, nsegs, L, nbody, n_cchunks;
     uint32_t groups_per_b, n_units;
     int stages;
+    int rb;                // 7-row blocks per slab: one TMA box / mbarrier hand-shake feeds rb bodies
     uint32_t seg_stride;   // bytes between the segments of one slab (multiple of 128)
     uint32_t row_bytes;    // CC * sizeof(TIn)
     uint32_t stage_bytes;  // nsegs * seg_stride
@@ -323,7 +324,7 @@ act1d_nlc_tma_kernel(const __grid_constant__ CUtensorMap map_x, TOut* __restrict
         fence_barrier_init();
     }
     __syncthreads();
-    const int n_slabs = p.nbody + 1;
+    const int n_slabs = (p.nbody + 1 + p.rb - 1) / p.rb;  // blocks: 1 window block + nbody bodies, rb per slab
     const uint32_t smem_base = smem_u32(smem);
     int st = 0;
     uint32_t ph = 0;
@@ -344,7 +345,7 @@ act1d_nlc_tma_kernel(const __grid_constant__ CUtensorMap map_x, TOut* __restrict
                 uint8_t* dst = smem + st * p.stage_bytes;
                 for (int s = lane; s < p.nsegs; s += 32)
                     tma_load_3d(dst + s * p.seg_stride, &map_x, &full[st], static_cast<int>(cch) * p.CC,
-                                row_base + s * p.L + 7 * q, static_cast<int>(b));
+                                row_base + s * p.L + 7 * p.rb * q, static_cast<int>(b));
                 if (++st == p.stages) { st = 0; ph ^= 1; }
             }
         }
@@ -387,28 +388,34 @@ act1d_nlc_tma_kernel(const __grid_constant__ CUtensorMap map_x, TOut* __restrict
         float2 nxt[7];
 #endif
         float2 vlast = splat(0.f), xlast = splat(0.f);
-        // slab 0: rows t0-7 .. t0-1; the window starts with rows t0-6 .. t0-1
+        // The unit's rows arrive as 7-row blocks: block 0 = rows t0-7 .. t0-1 (the window starts with rows t0-6 .. t0-1),
+        // block b+1 = the rows of body b.  A slab holds rb consecutive blocks of every segment; it is waited for at its
+        // first block and handed back to the producer after its last one.
+        const int last_blk = p.nbody;
+        int blk = 0, sub = 0;
+        auto release = [&]() {
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&empty[st]);
+            if (++st == p.stages) { st = 0; ph ^= 1; }
+            sub = 0;
+        };
         mbar_wait(&full[st], ph);
         {
             const uint32_t sp = smem_base + st * p.stage_bytes + my_off;
 #pragma unroll
             for (int j = 0; j < 6; ++j) xw[j] = SmemPair<TIn>::load(sp + (j + 1) * p.row_bytes);
         }
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&empty[st]);
-        if (++st == p.stages) { st = 0; ph ^= 1; }
+        if (p.rb == 1 || last_blk == 0) release(); else sub = 1;
+        blk = 1;
 #pragma unroll
         for (int s = 0; s < 7; ++s) acc[s] = splat(0.f);
-        // the slab of body b+1 is read into registers before body b is computed, so its mbarrier wait and shared-memory
-        // latency sit under ~350 instructions of FFMA2 / MUFU work
         auto fetch = [&](float2 (&dst)[7]) {
-            mbar_wait(&full[st], ph);
-            const uint32_t sp = smem_base + st * p.stage_bytes + my_off;
+            if (sub == 0) mbar_wait(&full[st], ph);
+            const uint32_t sp = smem_base + st * p.stage_bytes + my_off + sub * 7u * p.row_bytes;
 #pragma unroll
             for (int s = 0; s < 7; ++s) dst[s] = SmemPair<TIn>::load(sp + s * p.row_bytes);
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&empty[st]);
-            if (++st == p.stages) { st = 0; ph ^= 1; }
+            if (sub + 1 == p.rb || blk == last_blk) release(); else ++sub;
+            ++blk;
         };
 #if ACT_TMA_PREFETCH
         fetch(nxt);
@@ -699,11 +706,19 @@ static int launch_nlc_tma(const void* x, void* y, const float* alpha, const floa
     p.nsegs = ACT_TMA_COMPUTE / p.P;
     p.n_cchunks = static_cast<int>(C / CC);
     const int sms = device_sm_count();
-    const int64_t want_units = 2ll * 2 * sms;
-    static const int kL[] = {120, 92, 64, 50, 36, 22, 15, 8};
+    // Segment length L (L + 6 a multiple of 7): minimise waves x (rows marched per unit incl. the 7 warm-up rows), i.e.
+    // trade the per-segment warm-up (favours long segments) against the last-group padding and the tail wave of the
+    // persistent grid (favour many short units).  Ties go to the longer segment.
     int L = 8;
-    for (int cand : kL) {
-        if (B * ceil_div(T, (int64_t)p.nsegs * cand) * p.n_cchunks >= want_units) { L = cand; break; }
+    {
+        const int64_t ctas = (int64_t)ACT_TMA_MIN_CTAS * sms;
+        int64_t best = -1;
+        for (int cand = 120; cand >= 8; cand -= 7) {
+            const int64_t units_c = B * ceil_div(T, (int64_t)p.nsegs * cand) * p.n_cchunks;
+            const int64_t waves = ceil_div(units_c, ctas);
+            const int64_t cost = waves * (cand + 13);  // +6 rounding rows, +7 window rows
+            if (best < 0 || cost < best) { best = cost; L = cand; }
+        }
     }
     p.L = L;
     p.nbody = (L + 6) / 7;
@@ -713,15 +728,31 @@ static int launch_nlc_tma(const void* x, void* y, const float* alpha, const floa
     p.groups_per_b = static_cast<uint32_t>(groups);
     p.n_units = static_cast<uint32_t>(units);
     p.row_bytes = static_cast<uint32_t>(CC * sizeof(TIn));
-    p.seg_stride = static_cast<uint32_t>(round_up(7ll * p.row_bytes, 128));
-    p.stage_bytes = p.nsegs * p.seg_stride;
-    p.tx_bytes = p.nsegs * 7u * p.row_bytes;
     static const int ring_kb = []() {
         const char* e = getenv("BVG_ACT_SMEM_KB");
         const int kb = e ? atoi(e) : 0;
         return (kb >= 16 && kb <= 100) ? kb : BVG_ACT_SMEM_KB_DEFAULT;
     }();
-    int stages = static_cast<int>((ring_kb * 1024) / p.stage_bytes);
+    // 7-row blocks per slab: with one block per slab the producer warp issues nsegs small TMA boxes (7 rows x <= 128 B)
+    // per body and could not keep the ring full for the 21-segment C = 24 layout (ncu r01v: 13 % of the compute warps'
+    // samples on the slab barrier); larger boxes cut the TMA issue and mbarrier traffic by rb at the same ring bytes.
+    static const int rb_env = []() { const char* e = getenv("BVG_ACT_RB"); return e ? atoi(e) : 0; }();
+    int stages = 0;
+    p.rb = 1;
+    for (int rb : {2, 4, 1}) {
+        if (rb_env > 0 && rb != rb_env && rb != 1) continue;
+        if (rb > p.nbody + 1) continue;
+        const uint32_t seg_stride = static_cast<uint32_t>(round_up(7ll * rb * p.row_bytes, 128));
+        const int st_c = static_cast<int>((ring_kb * 1024) / (p.nsegs * seg_stride));
+        if (st_c >= 3 || rb == 1) {
+            p.rb = rb;
+            p.seg_stride = seg_stride;
+            stages = st_c;
+            break;
+        }
+    }
+    p.stage_bytes = p.nsegs * p.seg_stride;
+    p.tx_bytes = p.nsegs * 7u * p.rb * p.row_bytes;
     if (stages > ACT_TMA_MAX_STAGES) stages = ACT_TMA_MAX_STAGES;
     if (stages < 2) return 1;
     p.stages = stages;
@@ -733,7 +764,7 @@ static int launch_nlc_tma(const void* x, void* y, const float* alpha, const floa
     const uint64_t es = sizeof(TIn);
     cuuint64_t dims[3] = {(cuuint64_t)C, (cuuint64_t)T, (cuuint64_t)B};
     cuuint64_t strides[2] = {(cuuint64_t)C * es, (cuuint64_t)C * (cuuint64_t)T * es};
-    cuuint32_t box[3] = {(cuuint32_t)CC, 7, 1};
+    cuuint32_t box[3] = {(cuuint32_t)CC, (cuuint32_t)(7 * p.rb), 1};
     cuuint32_t estr[3] = {1, 1, 1};
     CUresult r = enc(&map, sizeof(TIn) == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3,
                      const_cast<void*>(x), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
