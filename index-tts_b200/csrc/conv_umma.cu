@@ -87,7 +87,6 @@ struct ConvUmmaParams {
     unsigned long long* trace;  // developer timeline buffer (bvg_debug_conv_trace) or null
     int trace_n;
     uint32_t bias_smem;  // bytes of the zero-padded bias copy in shared memory (0: read the bias from global memory)
-    int dbg;           // developer timing experiments (BVG_CONV_DBG): 1 = no output stores, 2 = no A loads, 4 = no chunk loads
     float out_scale;
 };
 
@@ -337,17 +336,13 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                 mbar_wait_warp(&a_empty[slot0 + sa], pa ^ 1);
                 if (kb == 0 && lane == 0) trace_ev(p, 0, it);
                 if (elect_one()) {
-                    if (p.dbg & 2) {
-                        mbar_arrive(&a_full[slot0 + sa]);
-                    } else {
-                        mbar_arrive_expect_tx(&a_full[slot0 + sa], p.mp * p.a_box_bytes);
-                        uint8_t* dst = sA + (slot0 + sa) * p.a_stage_bytes;
-                        tma_load_3d(dst, &map_x, &a_full[slot0 + sa], kb * UMMA_BLOCK_K, row0, b);
-                        // pair mode: the second halo box starts 128 rows (16 KB) further; the overlapping rows are
-                        // simply written twice with the same data
-                        if (p.mp == 2)
-                            tma_load_3d(dst + 16384, &map_x, &a_full[slot0 + sa], kb * UMMA_BLOCK_K, row0 + UMMA_BLOCK_M, b);
-                    }
+                    mbar_arrive_expect_tx(&a_full[slot0 + sa], p.mp * p.a_box_bytes);
+                    uint8_t* dst = sA + (slot0 + sa) * p.a_stage_bytes;
+                    tma_load_3d(dst, &map_x, &a_full[slot0 + sa], kb * UMMA_BLOCK_K, row0, b);
+                    // pair mode: the second halo box starts 128 rows (16 KB) further; the overlapping rows are
+                    // simply written twice with the same data
+                    if (p.mp == 2)
+                        tma_load_3d(dst + 16384, &map_x, &a_full[slot0 + sa], kb * UMMA_BLOCK_K, row0 + UMMA_BLOCK_M, b);
                 }
                 if (++sa == a_per) { sa = 0; pa ^= 1; }
                 if (!p.stationary) {
@@ -400,9 +395,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                     const int t0 = t00 + sub * UMMA_BLOCK_M;
                     const int slot = slot0 + s;
                     mbar_wait_warp(&ld_empty[slot], ps ^ 1);
-                    if ((p.dbg & 4) && elect_one()) {
-                        mbar_arrive(&ld_full[slot]);
-                    } else if (elect_one()) {
+                    if (elect_one()) {
                         mbar_arrive_expect_tx(&ld_full[slot], n_ld * EPI_LD_TILE_BYTES);
                         uint8_t* dst = sLd + slot * n_ld * EPI_LD_TILE_BYTES;
                         if (p.has_res) tma_load_4d(dst, &map_res, &ld_full[slot], c0 + c, phase, t0, b);
@@ -549,7 +542,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                 }
                 fence_proxy_async_smem();
                 __syncwarp();
-                if (lane == 0 && !(p.dbg & 1)) {
+                if (lane == 0) {
                     if (p.has_y32) tma_store_4d(&map_y32, st32 + ob * EPI_ST32_TILE_BYTES, c0 + c, phase, t0 + q * 32, b);
                     if (p.has_y16) tma_store_4d(&map_y16, st16 + ob * EPI_ST16_TILE_BYTES, c0 + c, phase, t0 + q * 32, b);
                     tma_store_commit();
@@ -702,10 +695,6 @@ int conv_umma_launch(const void* x, const void* w_packed, const float* bias, con
     p.ng = 1;
     p.trace = g_conv_trace;
     p.trace_n = g_conv_trace_n;
-    {
-        static const int dbg_env = []() { const char* e = getenv("BVG_CONV_DBG"); return e ? atoi(e) : 0; }();
-        p.dbg = dbg_env;
-    }
     p.has_res = residual != nullptr; p.has_acc = accum != nullptr;
     p.has_y32 = y_f32 != nullptr; p.has_y16 = y_bf16 != nullptr;
     const int n_ld = p.has_res + p.has_acc;
