@@ -254,8 +254,8 @@ def fold_conv1d_weight(w: torch.Tensor, dilation: int, fold: int) -> torch.Tenso
     return out
 
 
-# Fold AMP-block convs of stages with at most this many channels by FOLD_FACTOR when the folded conv needs at most
-# FOLD_MAX_TAPS taps (the folded GEMM does fold*taps'/k times the FLOPs on an otherwise idle tensor pipe; beyond ~5 taps
+# Fold AMP-block convs of stages with at most this many channels by FOLD_FACTOR (stages up to 48 channels by 2: measured
+# -10 % on their k = 7 layers, neutral elsewhere) when the folded conv needs at most FOLD_MAX_TAPS taps (the folded GEMM does fold*taps'/k times the FLOPs on an otherwise idle tensor pipe; beyond ~5 taps
 # the weights stop being shared-memory resident and the layer gets slower instead).  BVG_FOLD=0 switches it off.
 FOLD_MAX_CHANNELS = 32
 FOLD_FACTOR = 4
@@ -302,9 +302,9 @@ class _PackedGenerator:
             dst.k = int(m.kernel_size[0])
             dst.dilation = int(m.dilation[0])
             dst.fold = 0
-            r = FOLD_FACTOR
+            r = FOLD_FACTOR if dst.cin <= FOLD_MAX_CHANNELS else 2  # C = 24 -> 96 by 4, C = 48 -> 96 by 2
             if (fold_ok and not transposed and time_factor % r == 0 and dst.cin == dst.cout
-                    and dst.cin <= FOLD_MAX_CHANNELS and dst.k % 2 == 1
+                    and dst.cin * r <= 128 and dst.k % 2 == 1
                     and 2 * -(-((dst.k - 1) // 2 * dst.dilation) // r) + 1 <= FOLD_MAX_TAPS):
                 wf = fold_conv1d_weight(_effective_weight(m).detach().to(device=device, dtype=torch.float32),
                                         dst.dilation, r)
