@@ -262,6 +262,15 @@ FOLD_FACTOR = 4
 FOLD_MAX_TAPS = 5
 
 
+def _fold_max_taps(r: int, k: int) -> int:
+    """Measured per layer (gpurun r01, tools/layer_ab.py): folding by 4 pays up to 9 folded taps (the folded layer is a
+    C = 96 conv, weight-streaming in pair mode beyond 4 taps); folding by 2 pays up to 7 taps for k >= 7 but loses for
+    the k = 3, d = 5 layer.  More than 9 taps exceed the shared-memory plan of the conv kernel."""
+    if r >= 4:
+        return 9
+    return 7 if k >= 7 else FOLD_MAX_TAPS
+
+
 class _PackedGenerator:
     """Folded + packed weights of one BigVGAN on one device in one precision, and the C descriptor pointing at them."""
 
@@ -305,7 +314,7 @@ class _PackedGenerator:
             r = FOLD_FACTOR if dst.cin <= FOLD_MAX_CHANNELS else 2  # C = 24 -> 96 by 4, C = 48 -> 96 by 2
             if (fold_ok and not transposed and time_factor % r == 0 and dst.cin == dst.cout
                     and dst.cin * r <= 128 and dst.k % 2 == 1
-                    and 2 * -(-((dst.k - 1) // 2 * dst.dilation) // r) + 1 <= FOLD_MAX_TAPS):
+                    and 2 * -(-((dst.k - 1) // 2 * dst.dilation) // r) + 1 <= _fold_max_taps(r, dst.k)):
                 wf = fold_conv1d_weight(_effective_weight(m).detach().to(device=device, dtype=torch.float32),
                                         dst.dilation, r)
                 w = ops.pack_conv1d_weight(wf, precision)
