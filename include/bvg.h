@@ -47,7 +47,7 @@ typedef enum {
     BVG_ERR_WORKSPACE = -5    /* workspace too small */
 } bvg_status;
 
-typedef enum { BVG_F32 = 0, BVG_BF16 = 1 } bvg_dtype;
+typedef enum { BVG_F32 = 0, BVG_BF16 = 1, BVG_I16 = 2 /* PCM output of the tail kernel only */ } bvg_dtype;
 
 /* bvg_precision: arithmetic mode of the convolutions.
  *   BVG_EXACT_F32 : fp32 operands, fp32 FMA accumulation (CUDA cores), accurate sin  -> the fp32 parity mode
@@ -134,6 +134,11 @@ BVG_API int bvg_convtranspose1d_nlc_fwd(const void* x, const void* w_packed, con
  * y: fp32 [B,1,T]. */
 BVG_API int bvg_conv_post_fwd(const float* x, const float* w, const float* bias, float* y, int64_t B, int64_t T, int64_t Cin,
                       int k, int use_tanh, void* stream);
+/* Same layer with the caller's PCM conversion fused into the epilogue: replaces BV/bigvgan.py:379-384 followed by
+ * infer_v2.py:866 (clamp(32767 * wav, -32767, 32767)) and infer_v2.py:912 (.type(torch.int16), truncation toward zero).
+ * pcm: int16 [B,1,T]. */
+BVG_API int bvg_conv_post_pcm16_fwd(const float* x, const float* w, const float* bias, int16_t* pcm, int64_t B, int64_t T,
+                            int64_t Cin, int k, int use_tanh, void* stream);
 
 /* ---------------------------------------------------------------------------------------------------------- */
 /* whole generator (BV/bigvgan.py:360-386 BigVGAN.forward)                                                     */
@@ -181,6 +186,11 @@ BVG_API size_t bvg_workspace_bytes(const bvg_model_desc* m_host, int64_t B, int6
  * wav: fp32 [B, 1, T_mel * prod(upsample_rates)], values in [-1, 1].  m_host is a HOST struct of device pointers. */
 BVG_API int bvg_forward(const bvg_model_desc* m_host, const float* mel, int64_t mel_stride_b, int64_t mel_stride_c, float* wav,
                 int64_t B, int64_t T_mel, void* workspace, size_t workspace_bytes, void* stream);
+
+/* bvg_forward with 16-bit PCM output (bvg_conv_post_pcm16_fwd as the tail): pcm int16 [B, 1, T_mel * prod(rates)] holds
+ * exactly what infer_v2.py:860-866, 912 compute from the fp32 waveform. */
+BVG_API int bvg_forward_pcm16(const bvg_model_desc* m_host, const float* mel, int64_t mel_stride_b, int64_t mel_stride_c,
+                      int16_t* pcm, int64_t B, int64_t T_mel, void* workspace, size_t workspace_bytes, void* stream);
 
 /* ---------------------------------------------------------------------------------------------------------- */
 /* measurement: the same launch plan as bvg_forward with a CUDA event pair around every kernel launch (recorded on

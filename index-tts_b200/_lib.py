@@ -77,6 +77,8 @@ SIGNATURES = {
     "bvg_convtranspose1d_nlc_fwd": (c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_i64, c_i64, c_i64, c_int, c_int,
                                             c_int, c_vp]),
     "bvg_conv_post_fwd": (c_int, [c_vp, c_vp, c_vp, c_vp, c_i64, c_i64, c_i64, c_int, c_int, c_vp]),
+    "bvg_conv_post_pcm16_fwd": (c_int, [c_vp, c_vp, c_vp, c_vp, c_i64, c_i64, c_i64, c_int, c_int, c_vp]),
+    "bvg_forward_pcm16": (c_int, [C.POINTER(ModelDesc), c_vp, c_i64, c_i64, c_vp, c_i64, c_i64, c_vp, c_sz, c_vp]),
     "bvg_workspace_bytes": (c_sz, [C.POINTER(ModelDesc), c_i64, c_i64]),
     "bvg_forward": (c_int, [C.POINTER(ModelDesc), c_vp, c_i64, c_i64, c_vp, c_i64, c_i64, c_vp, c_sz, c_vp]),
     "bvg_forward_profile": (c_int, [C.POINTER(ModelDesc), c_vp, c_i64, c_i64, c_vp, c_i64, c_i64, c_vp, c_sz, c_vp,

@@ -362,10 +362,10 @@ class _PackedGenerator:
         _next_plan_id[0] += 1
         _PLANS[self.plan_id] = self
 
-    def run(self, mel: torch.Tensor) -> torch.Tensor:
+    def run(self, mel: torch.Tensor, pcm16: bool = False) -> torch.Tensor:
         lib = _lib.load()
         B, _, T = mel.shape
-        wav = torch.empty((B, 1, T * self.hop), dtype=torch.float32, device=mel.device)
+        wav = torch.empty((B, 1, T * self.hop), dtype=torch.int16 if pcm16 else torch.float32, device=mel.device)
         if B == 0 or T == 0:
             return wav
         if mel.stride(2) != 1:
@@ -375,9 +375,10 @@ class _PackedGenerator:
             _lib.check(-1, "bvg_workspace_bytes")
         ws = torch.empty(ws_bytes, dtype=torch.uint8, device=mel.device)  # per call: safe across host threads
         with torch.cuda.device(mel.device):
-            _lib.check(lib.bvg_forward(ctypes.byref(self.desc), mel.data_ptr(), mel.stride(0), mel.stride(1),
-                                       wav.data_ptr(), B, T, ws.data_ptr(), ws_bytes,
-                                       torch.cuda.current_stream().cuda_stream), "bvg_forward")
+            fn = lib.bvg_forward_pcm16 if pcm16 else lib.bvg_forward
+            _lib.check(fn(ctypes.byref(self.desc), mel.data_ptr(), mel.stride(0), mel.stride(1), wav.data_ptr(), B, T,
+                          ws.data_ptr(), ws_bytes, torch.cuda.current_stream().cuda_stream),
+                       "bvg_forward_pcm16" if pcm16 else "bvg_forward")
         return wav
 
 
@@ -417,6 +418,19 @@ def _vocoder_forward(mel: torch.Tensor, plan_id: int, hop: int) -> torch.Tensor:
 @_vocoder_forward.register_fake
 def _(mel, plan_id, hop):
     return mel.new_empty((mel.shape[0], 1, mel.shape[2] * hop), dtype=torch.float32)
+
+
+@torch.library.custom_op("bvg::vocoder_forward_pcm16", mutates_args=())
+def _vocoder_forward_pcm16(mel: torch.Tensor, plan_id: int, hop: int) -> torch.Tensor:
+    plan = _PLANS.get(plan_id)
+    if plan is None:
+        raise _lib.BvgError(f"bvg::vocoder_forward_pcm16: plan {plan_id} no longer exists")
+    return plan.run(mel, pcm16=True)
+
+
+@_vocoder_forward_pcm16.register_fake
+def _(mel, plan_id, hop):
+    return mel.new_empty((mel.shape[0], 1, mel.shape[2] * hop), dtype=torch.int16)
 
 
 class BigVGAN(
@@ -528,6 +542,21 @@ class BigVGAN(
             x = x.float()
         plan = self._plan(x.device)
         return _vocoder_forward(x, plan.plan_id, plan.hop)
+
+    def forward_pcm16(self, x):
+        """Extra (not in the reference): ``forward`` with the caller's PCM conversion fused into the tail kernel.
+        Returns the int16 ``[B, 1, T_mel * hop]`` tensor that ``infer_v2.py:860-866, 912`` compute from the waveform:
+        ``torch.clamp(32767 * wav, -32767.0, 32767.0).type(torch.int16)``."""
+        if x.dim() != 3 or x.shape[1] != self.h.num_mels:
+            raise ValueError(f"expected mel of shape [B, {self.h.num_mels}, T], got {tuple(x.shape)}")
+        if not x.is_cuda:
+            raise _lib.BvgError("BigVGAN.forward_pcm16: libbvg has no CPU path; move the module and the mel to a B200 "
+                                f"(got device {x.device})")
+        _lib.require_device(x.device.index if x.device.index is not None else torch.cuda.current_device())
+        if x.dtype != torch.float32:
+            x = x.float()
+        plan = self._plan(x.device)
+        return _vocoder_forward_pcm16(x, plan.plan_id, plan.hop)
 
     def remove_weight_norm(self):
         try:

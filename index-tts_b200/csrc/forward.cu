@@ -198,8 +198,9 @@ extern "C" size_t bvg_workspace_bytes(const bvg_model_desc* m, int64_t B, int64_
     return pl.total + 256;
 }
 
-extern "C" int bvg_forward(const bvg_model_desc* m, const float* mel, int64_t mel_stride_b, int64_t mel_stride_c,
-                           float* wav, int64_t B, int64_t T_mel, void* workspace, size_t workspace_bytes, void* stream) {
+// wav_dtype: BVG_F32 (the module's output) or BVG_I16 (the caller's PCM conversion fused into the tail kernel)
+static int forward_impl(const bvg_model_desc* m, const float* mel, int64_t mel_stride_b, int64_t mel_stride_c, void* wav,
+                        int wav_dtype, int64_t B, int64_t T_mel, void* workspace, size_t workspace_bytes, void* stream) {
     BVG_REQUIRE(m && mel && wav, BVG_ERR_INVALID, "bvg_forward: null pointer");
     BVG_REQUIRE(B >= 0 && T_mel >= 0, BVG_ERR_INVALID, "bvg_forward: negative shape");
     if (B == 0 || T_mel == 0) return BVG_OK;
@@ -332,7 +333,23 @@ extern "C" int bvg_forward(const bvg_model_desc* m, const float* mel, int64_t me
     const bvg_conv_desc& cp = m->conv_post;
     BVG_REQUIRE(cp.cout == 1 && cp.cin == C, BVG_ERR_UNSUPPORTED, "conv_post must map %d channels to 1", C);
     ProfScope ps(BVG_K_POST, -1, C, 1, cp.k, 1, B * T, 2.0 * C * cp.k * (double)B * T, es * (double)B * T * (C + 1.0), st);
-    return bvg_conv_post_fwd(reinterpret_cast<const float*>(ws + pl.off_r[0]), static_cast<const float*>(cp.w), cp.bias, wav, B, T, C, cp.k, m->use_tanh_at_final, stream);
+    const float* post_in = reinterpret_cast<const float*>(ws + pl.off_r[0]);
+    if (wav_dtype == BVG_I16)
+        return bvg_conv_post_pcm16_fwd(post_in, static_cast<const float*>(cp.w), cp.bias, static_cast<int16_t*>(wav), B, T, C,
+                                       cp.k, m->use_tanh_at_final, stream);
+    return bvg_conv_post_fwd(post_in, static_cast<const float*>(cp.w), cp.bias, static_cast<float*>(wav), B, T, C, cp.k,
+                             m->use_tanh_at_final, stream);
+}
+
+extern "C" int bvg_forward(const bvg_model_desc* m, const float* mel, int64_t mel_stride_b, int64_t mel_stride_c,
+                           float* wav, int64_t B, int64_t T_mel, void* workspace, size_t workspace_bytes, void* stream) {
+    return forward_impl(m, mel, mel_stride_b, mel_stride_c, wav, BVG_F32, B, T_mel, workspace, workspace_bytes, stream);
+}
+
+extern "C" int bvg_forward_pcm16(const bvg_model_desc* m, const float* mel, int64_t mel_stride_b, int64_t mel_stride_c,
+                                 int16_t* pcm, int64_t B, int64_t T_mel, void* workspace, size_t workspace_bytes,
+                                 void* stream) {
+    return forward_impl(m, mel, mel_stride_b, mel_stride_c, pcm, BVG_I16, B, T_mel, workspace, workspace_bytes, stream);
 }
 
 extern "C" int bvg_forward_profile(const bvg_model_desc* m, const float* mel, int64_t mel_stride_b, int64_t mel_stride_c,

@@ -125,9 +125,22 @@ int transpose_any(const void* src, int src_dtype, void* dst, int dst_dtype, int6
 // ------------------------------------------------------------------------------------------------------------
 constexpr int POST_MAX_W = 1024;  // Cin * k
 
+// TOut = float: the module's output.  TOut = int16_t: the caller's PCM conversion fused in (reference infer_v2.py:866,
+// 912: clamp(32767 * wav, -32767, 32767).type(int16), i.e. truncation toward zero).
+template <typename TOut>
+__device__ __forceinline__ TOut post_convert(float o);
+template <>
+__device__ __forceinline__ float post_convert<float>(float o) { return o; }
+template <>
+__device__ __forceinline__ int16_t post_convert<int16_t>(float o) {
+    const float p = fminf(fmaxf(32767.0f * o, -32767.0f), 32767.0f);
+    return static_cast<int16_t>(__float2int_rz(p));
+}
+
+template <typename TOut>
 __global__ void __launch_bounds__(256)
 conv_post_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
-                 float* __restrict__ y, int64_t T, int Cin, int k, int use_tanh) {
+                 TOut* __restrict__ y, int64_t T, int Cin, int k, int use_tanh) {
     __shared__ float ws[POST_MAX_W];  // ws[j*Cin + c] = w[c*k + j]
     for (int i = threadIdx.x; i < Cin * k; i += blockDim.x) {
         const int j = i / Cin, c = i % Cin;
@@ -157,7 +170,113 @@ conv_post_kernel(const float* __restrict__ x, const float* __restrict__ w, const
     float o = (acc0 + acc1) + (acc2 + acc3);
     if (bias) o += bias[0];
     o = use_tanh ? tanhf(o) : fminf(fmaxf(o, -1.0f), 1.0f);
-    y[b * T + t] = o;
+    y[b * T + t] = post_convert<TOut>(o);
+}
+
+// Tiled version for the generator's own tail (Cin = 24, k = 7 in bigvgan_v2_22khz_80band_256x).  The one-thread-per-
+// sample kernel above reads 7 rows x 96 B per thread with a 96-byte lane stride: 24 L1 wavefronts per load instruction,
+// 230 us at cfg2 against a 52 us HBM floor.  Here a CTA stages NT*R + K - 1 channels-last rows in shared memory with
+// coalesced 16-byte loads (row stride CIN + 1 words: with R odd the lane stride R*(CIN+1) is odd, so scalar LDS are
+// conflict free), every thread produces R consecutive samples from a sliding window of R + K - 1 rows (weights of one
+// channel quad live in registers across the window), and the results leave through shared memory as coalesced stores.
+// TOut = float: the module's output.  TOut = int16_t: the caller's PCM conversion (reference infer_v2.py:866, 912:
+// clamp(32767 * wav, -32767, 32767).type(int16), truncation toward zero) fused in.
+
+template <int CIN, int K, int R, int NT, typename TOut>
+__global__ void __launch_bounds__(NT)
+conv_post_tile_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
+                      TOut* __restrict__ y, int64_t T, int use_tanh) {
+    constexpr int TILE = NT * R, PAD = (K - 1) / 2, ROWS = TILE + K - 1, S = CIN + 1, Q = CIN / 4;
+    constexpr int XS_WORDS = (ROWS * S + 3) / 4 * 4;
+    extern __shared__ __align__(16) float post_smem[];
+    float* xs = post_smem;             // [ROWS][S]
+    float* wsm = post_smem + XS_WORDS;  // [K][CIN]: wsm[j*CIN + c] = w[c*K + j]
+    const int tid = threadIdx.x;
+    const int64_t b = blockIdx.y;
+    const int64_t t0 = (int64_t)blockIdx.x * TILE;
+    for (int i = tid; i < CIN * K; i += NT) wsm[i] = w[(i % CIN) * K + i / CIN];
+    {
+        const float* xb = x + b * T * CIN;
+        const int64_t row_lo = t0 - PAD;
+        constexpr int NV = ROWS * Q, U = 4;  // U independent 16-byte loads in flight per thread before the first store
+        for (int i0 = tid; i0 < NV; i0 += U * NT) {
+            float4 v[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int i = i0 + u * NT;
+                const int row = i / Q, q = i - row * Q;
+                const int64_t gr = row_lo + row;
+                v[u] = make_float4(0.f, 0.f, 0.f, 0.f);  // zero padding of the conv outside [0, T)
+                if (i < NV && gr >= 0 && gr < T) v[u] = __ldg(reinterpret_cast<const float4*>(xb + gr * CIN) + q);
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int i = i0 + u * NT;
+                if (i < NV) {
+                    const int row = i / Q, q = i - row * Q;
+                    float* d = xs + row * S + 4 * q;
+                    d[0] = v[u].x; d[1] = v[u].y; d[2] = v[u].z; d[3] = v[u].w;
+                }
+            }
+        }
+    }
+    __syncthreads();
+    float acc[R];
+#pragma unroll
+    for (int o = 0; o < R; ++o) acc[o] = 0.f;
+    const float* xr = xs + (R * tid) * S;
+#pragma unroll
+    for (int q = 0; q < Q; ++q) {
+        float4 wv[K];
+#pragma unroll
+        for (int j = 0; j < K; ++j) wv[j] = *reinterpret_cast<const float4*>(wsm + j * CIN + 4 * q);
+#pragma unroll
+        for (int rr = 0; rr < R + K - 1; ++rr) {
+            const float a0 = xr[rr * S + 4 * q], a1 = xr[rr * S + 4 * q + 1], a2 = xr[rr * S + 4 * q + 2],
+                        a3 = xr[rr * S + 4 * q + 3];
+#pragma unroll
+            for (int j = 0; j < K; ++j) {
+                const int o = rr - j;  // window row rr is tap j of output o
+                if (o >= 0 && o < R) acc[o] = fmaf(a3, wv[j].w, fmaf(a2, wv[j].z, fmaf(a1, wv[j].y, fmaf(a0, wv[j].x, acc[o]))));
+            }
+        }
+    }
+    __syncthreads();  // everyone is done reading xs: reuse it as the output staging row
+    const float bv = bias ? bias[0] : 0.f;
+#pragma unroll
+    for (int o = 0; o < R; ++o) {
+        float v = acc[o] + bv;
+        v = use_tanh ? tanhf(v) : fminf(fmaxf(v, -1.0f), 1.0f);
+        xs[R * tid + o] = v;
+    }
+    __syncthreads();
+    TOut* yb = y + b * T + t0;
+    for (int i = tid; i < TILE; i += NT)
+        if (t0 + i < T) yb[i] = post_convert<TOut>(xs[i]);
+}
+
+template <typename TOut>
+static int launch_conv_post(const float* x, const float* w, const float* bias, TOut* y, int64_t B, int64_t T, int64_t Cin,
+                            int k, int use_tanh, cudaStream_t st) {
+    if (Cin == 24 && k == 7) {
+        constexpr int CIN = 24, K = 7, R = 3, NT = 128;  // 39 KB of shared memory per CTA: 5 CTAs per SM
+        constexpr int XS_WORDS = ((NT * R + K - 1) * (CIN + 1) + 3) / 4 * 4;
+        constexpr int smem = (XS_WORDS + K * CIN) * 4;
+        auto kern = conv_post_tile_kernel<CIN, K, R, NT, TOut>;
+        static bool configured = false;  // idempotent attribute; a race only repeats the call
+        if (!configured) {
+            BVG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+            configured = true;
+        }
+        dim3 grid((unsigned)ceil_div(T, (int64_t)NT * R), (unsigned)B);
+        kern<<<grid, NT, smem, st>>>(x, w, bias, y, T, use_tanh);
+        BVG_LAUNCH_CHECK("conv_post_tile_kernel");
+        return BVG_OK;
+    }
+    dim3 grid((unsigned)ceil_div(T, 256), (unsigned)B);
+    conv_post_kernel<TOut><<<grid, 256, 0, st>>>(x, w, bias, y, T, (int)Cin, k, use_tanh);
+    BVG_LAUNCH_CHECK("conv_post_kernel");
+    return BVG_OK;
 }
 
 }  // namespace bvg
@@ -225,15 +344,26 @@ extern "C" int bvg_nlc_to_ncl(const void* x, int x_dtype, void* y, int y_dtype, 
     return transpose_any(x, x_dtype, y, y_dtype, B, T, C, T * C, C, static_cast<cudaStream_t>(stream));
 }
 
+static int conv_post_checks(const void* x, const void* w, const void* y, int64_t B, int64_t Cin, int k, const char* who) {
+    BVG_REQUIRE(x && w && y, BVG_ERR_INVALID, "%s: null pointer", who);
+    BVG_REQUIRE(Cin % 4 == 0 && Cin * k <= POST_MAX_W && k % 2 == 1, BVG_ERR_UNSUPPORTED, "%s: Cin=%lld k=%d unsupported", who,
+                (long long)Cin, k);
+    BVG_REQUIRE(B < 65536, BVG_ERR_UNSUPPORTED, "%s: B too large", who);
+    return BVG_OK;
+}
+
 extern "C" int bvg_conv_post_fwd(const float* x, const float* w, const float* bias, float* y, int64_t B, int64_t T,
                                  int64_t Cin, int k, int use_tanh, void* stream) {
-    BVG_REQUIRE(x && w && y, BVG_ERR_INVALID, "bvg_conv_post_fwd: null pointer");
-    BVG_REQUIRE(Cin % 4 == 0 && Cin * k <= POST_MAX_W && k % 2 == 1, BVG_ERR_UNSUPPORTED,
-                "bvg_conv_post_fwd: Cin=%lld k=%d unsupported", (long long)Cin, k);
-    BVG_REQUIRE(B < 65536, BVG_ERR_UNSUPPORTED, "bvg_conv_post_fwd: B too large");
+    const int rc = conv_post_checks(x, w, y, B, Cin, k, "bvg_conv_post_fwd");
+    if (rc != BVG_OK) return rc;
     if (B == 0 || T == 0) return BVG_OK;
-    dim3 grid((unsigned)ceil_div(T, 256), (unsigned)B);
-    conv_post_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(x, w, bias, y, T, (int)Cin, k, use_tanh);
-    BVG_LAUNCH_CHECK("conv_post_kernel");
-    return BVG_OK;
+    return launch_conv_post<float>(x, w, bias, y, B, T, Cin, k, use_tanh, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int bvg_conv_post_pcm16_fwd(const float* x, const float* w, const float* bias, int16_t* pcm, int64_t B, int64_t T,
+                                       int64_t Cin, int k, int use_tanh, void* stream) {
+    const int rc = conv_post_checks(x, w, pcm, B, Cin, k, "bvg_conv_post_pcm16_fwd");
+    if (rc != BVG_OK) return rc;
+    if (B == 0 || T == 0) return BVG_OK;
+    return launch_conv_post<int16_t>(x, w, bias, pcm, B, T, Cin, k, use_tanh, static_cast<cudaStream_t>(stream));
 }

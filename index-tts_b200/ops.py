@@ -208,15 +208,19 @@ def convtranspose1d_nlc(x: torch.Tensor, w_packed: torch.Tensor, bias: Optional[
     return y32 if out_f32 else y16
 
 
-def conv_post(x_nlc: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor], use_tanh: bool) -> torch.Tensor:
+def conv_post(x_nlc: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor], use_tanh: bool,
+              pcm16: bool = False) -> torch.Tensor:
+    """``conv_post`` + clamp / tanh (reference bigvgan.py:379-384) on a channels-last fp32 tensor.  ``pcm16=True`` also
+    applies the caller's ``clamp(32767 * wav, -32767, 32767).type(torch.int16)`` (infer_v2.py:866, 912) in the kernel."""
     _require_cuda(x_nlc, "conv_post")
     x_nlc = x_nlc.contiguous()
     B, T, Cin = x_nlc.shape
     w = w.detach().float().contiguous()
-    y = torch.empty((B, 1, T), dtype=torch.float32, device=x_nlc.device)
+    y = torch.empty((B, 1, T), dtype=torch.int16 if pcm16 else torch.float32, device=x_nlc.device)
+    fn = _lib.load().bvg_conv_post_pcm16_fwd if pcm16 else _lib.load().bvg_conv_post_fwd
     with torch.cuda.device(x_nlc.device):
-        check(_lib.load().bvg_conv_post_fwd(x_nlc.data_ptr(), w.data_ptr(), _ptr(bias), y.data_ptr(), B, T, Cin,
-                                            w.shape[-1], int(bool(use_tanh)), _stream()), "bvg_conv_post_fwd")
+        check(fn(x_nlc.data_ptr(), w.data_ptr(), _ptr(bias), y.data_ptr(), B, T, Cin, w.shape[-1], int(bool(use_tanh)),
+                 _stream()), "bvg_conv_post_pcm16_fwd" if pcm16 else "bvg_conv_post_fwd")
     return y
 
 

@@ -89,5 +89,9 @@ def test_infer_v2_vocoder_tail_unchanged():
         assert snr_db(ref, got) >= 80.0
         pcm = wav.type(torch.int16)                                          # infer_v2.py:912
         assert int((pcm.cpu().numpy().astype(np.int64) - np.round(ref).astype(np.int64)).__abs__().max()) <= 4
+        # the same conversion fused into the tail kernel -- identical bits, non-contiguous mel included
+        with torch.no_grad():
+            fused = self_bigvgan.forward_pcm16(vc_target.float()).squeeze().unsqueeze(0)
+        assert fused.dtype == torch.int16 and torch.equal(fused, pcm)
     finally:
         dropin.uninstall()

@@ -74,6 +74,30 @@ def test_full_generator_golden(golden_dir, full_models):
         _check_bf16(g[f"wav_{tag}"], wav, f"full/{tag}")
 
 
+def test_forward_pcm16_equals_callers_conversion(golden_dir, full_models):
+    """bvg_forward_pcm16 == infer_v2.py:866 + :912 applied to bvg_forward's waveform, both precisions, incl. the clamp."""
+    g = np.load(os.path.join(golden_dir, "full_forward.npz"))
+    _, m = full_models
+    for prec in ("fp32", "bf16"):
+        m.set_precision(prec)
+        for scale in (1.0, 40.0):  # 40x: the random-init waveform (max 0.05) reaches the clamp
+            mel = torch.from_numpy(g["mel_a"]).cuda()
+            with torch.no_grad():
+                w0 = m.conv_post.weight.detach().clone()
+                m.conv_post.weight.mul_(scale)
+                try:
+                    wav = m(mel)
+                    pcm = m.forward_pcm16(mel)
+                finally:
+                    m.conv_post.weight.copy_(w0)
+            assert pcm.dtype == torch.int16 and pcm.shape == wav.shape
+            assert torch.equal(pcm, torch.clamp(32767 * wav, -32767.0, 32767.0).type(torch.int16))
+            if scale > 1.0:
+                assert int(pcm.abs().max()) == 32767
+    m.set_precision("fp32")
+    assert m.forward_pcm16(torch.zeros(0, 80, 5, device="cuda")).shape == (0, 1, 1280)
+
+
 def test_full_generator_clamp_path(golden_dir):
     """1.3x weights + log-mel-like input: 16 % of the samples hit the final clamp(-1, 1)."""
     g = np.load(os.path.join(golden_dir, "full_forward.npz"))

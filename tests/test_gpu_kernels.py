@@ -229,6 +229,36 @@ def test_conv_post_clamp_and_tanh(ops):
     np.testing.assert_allclose(y, np.tanh(ref), atol=2e-6)
 
 
+@pytest.mark.parametrize("B,T", [(1, 1), (1, 5), (2, 383), (1, 384), (2, 385), (3, 1283), (1, 20000)])
+def test_conv_post_tiled_edges_and_pcm16(ops, B, T):
+    """The generator's own tail shape (24 -> 1, k = 7) runs the tiled kernel: tile edges (384 samples per CTA), T shorter
+    than the kernel, batch > 1; and the PCM mode equals infer_v2.py:866 + :912 applied to the fp32 output bit for bit."""
+    rng = np.random.default_rng(100 + T)
+    x = rng.standard_normal((B, 24, T)).astype(np.float32)
+    w = rng.standard_normal((1, 24, 7)).astype(np.float32) * 0.1
+    bias = rng.standard_normal(1).astype(np.float32) * 0.1
+    ref = O.conv1d(x.astype(np.float64), w.astype(np.float64), bias.astype(np.float64))
+    xn = _t(np.transpose(x, (0, 2, 1)))
+    y = ops.conv_post(xn, _t(w), _t(bias), False)
+    assert tuple(y.shape) == (B, 1, T)
+    np.testing.assert_allclose(y.cpu().numpy(), np.clip(ref, -1, 1), atol=2e-6)
+    pcm = ops.conv_post(xn, _t(w), _t(bias), False, pcm16=True)
+    assert pcm.dtype == torch.int16 and tuple(pcm.shape) == (B, 1, T)
+    want = torch.clamp(32767 * y, -32767.0, 32767.0).type(torch.int16)
+    assert torch.equal(pcm, want)
+    if T >= 383:
+        assert int(pcm.abs().max()) == 32767  # the clamp is exercised
+    # a shape the tiled kernel does not cover goes through the generic kernel, same contract
+    x2 = rng.standard_normal((B, 8, T)).astype(np.float32)
+    w2 = rng.standard_normal((1, 8, 3)).astype(np.float32) * 0.3
+    ref2 = O.conv1d(x2.astype(np.float64), w2.astype(np.float64), None)
+    xn2 = _t(np.transpose(x2, (0, 2, 1)))
+    y2 = ops.conv_post(xn2, _t(w2), None, False)
+    np.testing.assert_allclose(y2.cpu().numpy(), np.clip(ref2, -1, 1), atol=2e-6)
+    assert torch.equal(ops.conv_post(xn2, _t(w2), None, False, pcm16=True),
+                       torch.clamp(32767 * y2, -32767.0, 32767.0).type(torch.int16))
+
+
 def test_errors_are_loud(ops):
     from index_tts_b200 import _lib
     with pytest.raises(_lib.BvgError):

@@ -28,4 +28,10 @@ tot = collections.Counter()
 for (kind, stage, k), (n, ms) in agg.items():
     tot[kind] += ms
     print(f"{kind:7s} st{stage:2d} k{k:2d} n={n:2d} {ms:7.3f} ms  ({ms / n * 1e3:6.1f} us each)")
+if os.environ.get("LAYER_AB_DETAIL"):
+    # every launch against its own roofline: max(flops / sustained bf16 peak, bytes / HBM)
+    for r, ms in zip(recs, best):
+        floor = max(r["flops"] / 1396.8e12, r["bytes"] / 6555.2e9) * 1e3
+        print(f"  {r['kind'][:6]:7s} st{r['stage']:2d} C{r['cin']:4d} k{r['k']:2d} d{r['dilation']} {ms * 1e3:7.1f} us  floor {floor * 1e3:6.1f} us"
+              f"  frac {floor / ms if ms else 0:4.2f}  lost {1e3 * (ms - floor):6.1f} us")
 print("totals:", {k: round(v, 3) for k, v in tot.items()}, "sum", round(sum(tot.values()), 3))
