@@ -90,6 +90,15 @@ BVG_API int bvg_activation1d_fwd(const void* x, void* y, const float* alpha_log,
 BVG_API int bvg_activation1d_nlc_fwd(const void* x, int x_dtype, void* y, int y_dtype, const float* alpha_log,
                              const float* beta_log, int64_t B, int64_t T, int64_t C, int precise, void* stream);
 
+/* n_heads Activation1d of the SAME input with different snake parameters: ys[h] = Activation1d(x; alphas_log[h],
+ * betas_log[h]).  The three AMP blocks of a stage start with exactly this (BV/bigvgan.py:369-374 applies
+ * resblocks[3i+j] to one x; AMPBlock1.forward :132-141 begins with a1(x)).  Groups of three heads with fp32 input run as
+ * one kernel that computes the (parameter independent) 2x up-sampler once; ys, alphas_log, betas_log are HOST arrays of
+ * n_heads device pointers.  Results are bit-identical to n_heads bvg_activation1d_nlc_fwd calls. */
+BVG_API int bvg_activation1d_nlc_multi_fwd(const void* x, int x_dtype, void* const* ys, int y_dtype,
+                                   const float* const* alphas_log, const float* const* betas_log, int n_heads, int64_t B,
+                                   int64_t T, int64_t C, int precise, void* stream);
+
 /* ---------------------------------------------------------------------------------------------------------- */
 /* weight preparation (BV/bigvgan.py:388-400 remove_weight_norm is where the host calls these)                 */
 

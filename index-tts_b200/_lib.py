@@ -67,6 +67,8 @@ SIGNATURES = {
     "bvg_reset_launch_count": (None, []),
     "bvg_activation1d_fwd": (c_int, [c_vp, c_vp, c_vp, c_vp, c_i64, c_i64, c_i64, c_i64, c_i64, c_int, c_int, c_vp]),
     "bvg_activation1d_nlc_fwd": (c_int, [c_vp, c_int, c_vp, c_int, c_vp, c_vp, c_i64, c_i64, c_i64, c_int, c_vp]),
+    "bvg_activation1d_nlc_multi_fwd": (c_int, [c_vp, c_int, C.POINTER(c_vp), c_int, C.POINTER(c_vp), C.POINTER(c_vp), c_int,
+                                               c_i64, c_i64, c_i64, c_int, c_vp]),
     "bvg_fold_weight_norm": (c_int, [c_vp, c_vp, c_vp, c_i64, c_i64, c_vp]),
     "bvg_pack_conv1d_weight": (c_int, [c_vp, c_vp, c_i64, c_i64, c_i64, c_int, c_vp]),
     "bvg_pack_convtranspose1d_weight": (c_int, [c_vp, c_vp, c_i64, c_i64, c_i64, c_i64, c_int, c_vp]),

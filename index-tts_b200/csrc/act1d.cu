@@ -106,17 +106,18 @@ struct ActEdge {
 // pending outputs y[m-3 .. m+3] (y[i] = sum_k g[k] v[2i+k-5]; v[2m] carries tap 2(m-i)+5, v[2m+1] tap 2(m-i)+6), so
 // the twelve FFMA2 of a step are mutually independent (no 12-deep dependent chain) and only seven accumulators live
 // in registers instead of a 14-entry history of the activated signal.  acc[(s+j+3)%7] holds y[m+j] at step s.
-template <typename TOut, bool PRECISE, bool EDGE, bool FIRST>
-__device__ __forceinline__ void act1d_nlc_body(float2 (&xw)[7], float2 (&acc)[7], const float2 (&cur)[7], float2& vlast,
-                                               const SnakeCoef& coef, const ActEdge& e, int g0, uint8_t*& yp,
-                                               int64_t row_bytes) {
+// NH > 1 ("heads"): the three AMP blocks of a stage apply their first Activation1d to the SAME tensor with different
+// alpha / beta (reference bigvgan.py:369-374 calls resblocks[i*3+j](x) on one x).  The up-sampler does not depend on the
+// snake parameters, so one pass computes it once and runs NH snake + low-pass pipelines on it: 12 + 16 NH packed FP32
+// operations per row instead of 28 NH, and x is read once.  Head h stores at yp + ydelta[h] (ydelta[0] = 0).
+template <typename TOut, bool PRECISE, bool EDGE, bool FIRST, int NH>
+__device__ __forceinline__ void act1d_nlc_body(float2 (&xw)[7], float2 (&acc)[NH][7], const float2 (&cur)[7],
+                                               float2 (&vlast)[NH], const SnakeCoef (&coef)[NH], const ActEdge& e, int g0,
+                                               uint8_t*& yp, int64_t row_bytes, const int64_t (&ydelta)[NH]) {
     const float2 E0 = splat(2.f * BVG_F0), E1 = splat(2.f * BVG_F1), E2 = splat(2.f * BVG_F2),
                  E3 = splat(2.f * BVG_F3), E4 = splat(2.f * BVG_F4), E5 = splat(2.f * BVG_F5);
     const float2 G0 = splat(BVG_F0), G1 = splat(BVG_F1), G2 = splat(BVG_F2), G3 = splat(BVG_F3), G4 = splat(BVG_F4),
                  G5 = splat(BVG_F5);
-    // fast mode: the constant term of sin^2 = (1 - cos)/2 passes the unit-DC-gain low-pass unchanged, so it seeds
-    // every accumulator instead of being added per sample
-    const float2 hoisted_c = PRECISE ? splat(0.f) : coef.invb;
 #pragma unroll
     for (int s = 0; s < 7; ++s) {
         const int g = g0 + s;
@@ -135,47 +136,53 @@ __device__ __forceinline__ void act1d_nlc_body(float2 (&xw)[7], float2 (&acc)[7]
         uo = ffma2(E2, xp2, uo);
         ue = ffma2(E1, xp2, ue);
         uo = ffma2(E0, xp3, uo);
-        float2 a = snake2<PRECISE>(ue, coef);
-        float2 o = snake2<PRECISE>(uo, coef);
-        if (EDGE) {
-            if (g >= e.m_valid) {  // m >= T: replicate padding of the 2x signal on the right: v[2T-1]
-                a = vlast;
-                o = vlast;
-            } else {
-                vlast = o;
+#pragma unroll
+        for (int h = 0; h < NH; ++h) {
+            // fast mode: the constant term of sin^2 = (1 - cos)/2 passes the unit-DC-gain low-pass unchanged, so it
+            // seeds every accumulator instead of being added per sample
+            const float2 hoisted_c = PRECISE ? splat(0.f) : coef[h].invb;
+            float2 a = snake2<PRECISE>(ue, coef[h]);
+            float2 o = snake2<PRECISE>(uo, coef[h]);
+            if (EDGE) {
+                if (g >= e.m_valid) {  // m >= T: replicate padding of the 2x signal on the right: v[2T-1]
+                    a = vlast[h];
+                    o = vlast[h];
+                } else {
+                    vlast[h] = o;
+                }
             }
-        }
-        float2& yp3 = acc[(s + 6) % 7];
-        float2& yp2 = acc[(s + 5) % 7];
-        float2& yp1 = acc[(s + 4) % 7];
-        float2& y00 = acc[(s + 3) % 7];
-        float2& ym1 = acc[(s + 2) % 7];
-        float2& ym2 = acc[(s + 1) % 7];
-        float2& ym3 = acc[(s + 0) % 7];
-        if (EDGE && FIRST && s == 3 && e.first_seg) {
-            // m == 0: replicate padding on the left, v[n < 0] = v[0]: the virtual pairs m = -3, -2, -1 are (a, a)
-            const float2 g0a = ffma2(G0, a, hoisted_c);
-            const float2 g12 = splat(BVG_F1 + BVG_F2), g34 = splat(BVG_F3 + BVG_F4);
-            yp2 = g0a;                                     // y[2]: pair -1 tap 0
-            yp1 = ffma2(g12, a, g0a);                      // y[1]: pair -2 tap 0, pair -1 taps 1,2
-            y00 = ffma2(g34, a, ffma2(g12, a, g0a));       // y[0]: pair -3 tap 0, pair -2 taps 1,2, pair -1 taps 3,4
-            // (whatever steps 0..2 scattered into these three from the clamped-x pairs is discarded here)
-        }
-        yp3 = ffma2(G0, o, hoisted_c);
-        yp2 = ffma2(G1, a, yp2);
-        yp1 = ffma2(G3, a, yp1);
-        y00 = ffma2(G5, a, y00);
-        ym1 = ffma2(G4, a, ym1);
-        ym2 = ffma2(G2, a, ym2);
-        ym3 = ffma2(G0, a, ym3);
-        yp2 = ffma2(G2, o, yp2);
-        yp1 = ffma2(G4, o, yp1);
-        y00 = ffma2(G5, o, y00);
-        ym1 = ffma2(G3, o, ym1);
-        ym2 = ffma2(G1, o, ym2);
-        if (!FIRST || s == 6) {
-            const int i = g - 6;  // output row relative to t0
-            if (!EDGE || i < e.n_out) PairIO<TOut>::store(reinterpret_cast<TOut*>(yp), ym3);
+            float2& yp3 = acc[h][(s + 6) % 7];
+            float2& yp2 = acc[h][(s + 5) % 7];
+            float2& yp1 = acc[h][(s + 4) % 7];
+            float2& y00 = acc[h][(s + 3) % 7];
+            float2& ym1 = acc[h][(s + 2) % 7];
+            float2& ym2 = acc[h][(s + 1) % 7];
+            float2& ym3 = acc[h][(s + 0) % 7];
+            if (EDGE && FIRST && s == 3 && e.first_seg) {
+                // m == 0: replicate padding on the left, v[n < 0] = v[0]: the virtual pairs m = -3, -2, -1 are (a, a)
+                const float2 g0a = ffma2(G0, a, hoisted_c);
+                const float2 g12 = splat(BVG_F1 + BVG_F2), g34 = splat(BVG_F3 + BVG_F4);
+                yp2 = g0a;                                     // y[2]: pair -1 tap 0
+                yp1 = ffma2(g12, a, g0a);                      // y[1]: pair -2 tap 0, pair -1 taps 1,2
+                y00 = ffma2(g34, a, ffma2(g12, a, g0a));       // y[0]: pair -3 tap 0, pair -2 taps 1,2, pair -1 taps 3,4
+                // (whatever steps 0..2 scattered into these three from the clamped-x pairs is discarded here)
+            }
+            yp3 = ffma2(G0, o, hoisted_c);
+            yp2 = ffma2(G1, a, yp2);
+            yp1 = ffma2(G3, a, yp1);
+            y00 = ffma2(G5, a, y00);
+            ym1 = ffma2(G4, a, ym1);
+            ym2 = ffma2(G2, a, ym2);
+            ym3 = ffma2(G0, a, ym3);
+            yp2 = ffma2(G2, o, yp2);
+            yp1 = ffma2(G4, o, yp1);
+            y00 = ffma2(G5, o, y00);
+            ym1 = ffma2(G3, o, ym1);
+            ym2 = ffma2(G1, o, ym2);
+            if (!FIRST || s == 6) {
+                const int i = g - 6;  // output row relative to t0
+                if (!EDGE || i < e.n_out) PairIO<TOut>::store(reinterpret_cast<TOut*>(yp + ydelta[h]), ym3);
+            }
         }
         yp += row_bytes;  // running byte pointer (row g - 6 of the segment): one 64-bit add per row, no multiply per store
     }
@@ -200,14 +207,16 @@ __device__ __forceinline__ void act1d_nlc_segment(const TIn* __restrict__ xb, TO
     // x window: x[m+j], j=-3..3, lives in xw[(s+j+3)%7] at step s of a 7-step body; pair m in ve/vo[s].
     // Loads run two 7-row bodies (~14 rows, > 1 us of work per warp) ahead of their use: global latency is hidden by
     // the register prefetch queue cur <- nxt <- nxt2 rather than by occupancy (2 CTAs/SM at ~110 registers).
-    float2 xw[7], acc[7], cur[7], nxt[7], nxt2[7];
-    float2 vlast = splat(0.f);
+    float2 xw[7], acc[1][7], cur[7], nxt[7], nxt2[7];
+    float2 vlast[1] = {splat(0.f)};
+    const SnakeCoef coefs[1] = {coef};
+    const int64_t ydelta[1] = {0};
 #pragma unroll
     for (int j = 0; j < 6; ++j) xw[j] = ldx(j);
 #pragma unroll
     for (int s = 0; s < 7; ++s) {
         cur[s] = ldx(6 + s);
-        acc[s] = splat(0.f);
+        acc[0][s] = splat(0.f);
     }
     const int nbody = (L + 6) / 7;
 #pragma unroll
@@ -216,7 +225,7 @@ __device__ __forceinline__ void act1d_nlc_segment(const TIn* __restrict__ xb, TO
     for (int s = 0; s < 7; ++s) nxt2[s] = nbody > 2 ? ldx(20 + s) : splat(0.f);
     const int64_t row_bytes = (int64_t)C * (int64_t)sizeof(TOut);
     uint8_t* yp = reinterpret_cast<uint8_t*>(yrel) - 6 * row_bytes;  // row -6: never dereferenced before row 0
-    act1d_nlc_body<TOut, PRECISE, EDGE, true>(xw, acc, cur, vlast, coef, e, 0, yp, row_bytes);
+    act1d_nlc_body<TOut, PRECISE, EDGE, true, 1>(xw, acc, cur, vlast, coefs, e, 0, yp, row_bytes, ydelta);
 #pragma unroll 1
     for (int body = 1; body < nbody; ++body) {
         const int g0 = 7 * body;
@@ -226,7 +235,7 @@ __device__ __forceinline__ void act1d_nlc_segment(const TIn* __restrict__ xb, TO
 #pragma unroll
             for (int s = 0; s < 7; ++s) nxt2[s] = ldx(g0 + 20 + s);
         }
-        act1d_nlc_body<TOut, PRECISE, EDGE, false>(xw, acc, cur, vlast, coef, e, g0, yp, row_bytes);
+        act1d_nlc_body<TOut, PRECISE, EDGE, false, 1>(xw, acc, cur, vlast, coefs, e, g0, yp, row_bytes, ydelta);
     }
 }
 
@@ -305,10 +314,20 @@ struct SmemPair<__nv_bfloat16> {
     }
 };
 
-template <typename TIn, typename TOut, bool PRECISE>
-__global__ void __launch_bounds__(ACT_TMA_THREADS, ACT_TMA_MIN_CTAS)
-act1d_nlc_tma_kernel(const __grid_constant__ CUtensorMap map_x, TOut* __restrict__ y, const float* __restrict__ alpha,
-                     const float* __restrict__ beta, const __grid_constant__ ActTmaParams p) {
+// Outputs and snake parameters of the NH heads of one launch (NH = 1: the plain Activation1d).
+template <int NH>
+struct ActHeads {
+    void* y[NH];
+    const float* alpha[NH];
+    const float* beta[NH];
+};
+// CTAs per SM: the three-head body keeps 21 accumulators live (~150 registers), one CTA per SM
+constexpr int act_tma_min_ctas(int nh) { return nh == 1 ? ACT_TMA_MIN_CTAS : 1; }
+
+template <typename TIn, typename TOut, bool PRECISE, int NH>
+__global__ void __launch_bounds__(ACT_TMA_THREADS, act_tma_min_ctas(NH))
+act1d_nlc_tma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ ActHeads<NH> hd,
+                     const __grid_constant__ ActTmaParams p) {
     extern __shared__ uint8_t act_smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(act_smem_raw) + 127) & ~uintptr_t(127));
     uint64_t* full = reinterpret_cast<uint64_t*>(smem + p.stages * p.stage_bytes);
@@ -372,8 +391,14 @@ act1d_nlc_tma_kernel(const __grid_constant__ CUtensorMap map_x, TOut* __restrict
         const bool interior = (t0 > 0) && (t0 + L + 6 <= T);
         const bool edge_path = __any_sync(0xffffffffu, active && !interior);
         const int ch = static_cast<int>(cch) * p.CC + 2 * pair;
-        const SnakeCoef coef = make_coef<PRECISE>(alpha[ch], alpha[ch + 1], beta[ch], beta[ch + 1]);
-        TOut* yrel = y + (static_cast<int64_t>(b) * T + t0) * C + ch;
+        SnakeCoef coef[NH];
+        int64_t ydelta[NH];
+#pragma unroll
+        for (int h = 0; h < NH; ++h) {
+            coef[h] = make_coef<PRECISE>(hd.alpha[h][ch], hd.alpha[h][ch + 1], hd.beta[h][ch], hd.beta[h][ch + 1]);
+            ydelta[h] = static_cast<const uint8_t*>(hd.y[h]) - static_cast<const uint8_t*>(hd.y[0]);
+        }
+        TOut* yrel = static_cast<TOut*>(hd.y[0]) + (static_cast<int64_t>(b) * T + t0) * C + ch;
         const int64_t row_bytes = static_cast<int64_t>(C) * static_cast<int64_t>(sizeof(TOut));
         uint8_t* yp = reinterpret_cast<uint8_t*>(yrel) - 6 * row_bytes;  // row -6: never dereferenced before row 0
 
@@ -383,11 +408,13 @@ act1d_nlc_tma_kernel(const __grid_constant__ CUtensorMap map_x, TOut* __restrict
         e.n_out = static_cast<int>(min(static_cast<int64_t>(L), T - t0));
         e.first_seg = (t0 == 0);
 
-        float2 xw[7], acc[7], cur[7];
+        float2 xw[7], acc[NH][7], cur[7];
 #if ACT_TMA_PREFETCH
         float2 nxt[7];
 #endif
-        float2 vlast = splat(0.f), xlast = splat(0.f);
+        float2 vlast[NH], xlast = splat(0.f);
+#pragma unroll
+        for (int h = 0; h < NH; ++h) vlast[h] = splat(0.f);
         // The unit's rows arrive as 7-row blocks: block 0 = rows t0-7 .. t0-1 (the window starts with rows t0-6 .. t0-1),
         // block b+1 = the rows of body b.  A slab holds rb consecutive blocks of every segment; it is waited for at its
         // first block and handed back to the producer after its last one.
@@ -408,7 +435,9 @@ act1d_nlc_tma_kernel(const __grid_constant__ CUtensorMap map_x, TOut* __restrict
         if (p.rb == 1 || last_blk == 0) release(); else sub = 1;
         blk = 1;
 #pragma unroll
-        for (int s = 0; s < 7; ++s) acc[s] = splat(0.f);
+        for (int h = 0; h < NH; ++h)
+#pragma unroll
+            for (int s = 0; s < 7; ++s) acc[h][s] = splat(0.f);
         auto fetch = [&](float2 (&dst)[7]) {
             if (sub == 0) mbar_wait(&full[st], ph);
             const uint32_t sp = smem_base + st * p.stage_bytes + my_off + sub * 7u * p.row_bytes;
@@ -443,15 +472,15 @@ act1d_nlc_tma_kernel(const __grid_constant__ CUtensorMap map_x, TOut* __restrict
 #pragma unroll
                         for (int j = 0; j < 6; ++j) xw[j] = cur[0];
                     }
-                    act1d_nlc_body<TOut, PRECISE, true, true>(xw, acc, cur, vlast, coef, e, 0, yp, row_bytes);
+                    act1d_nlc_body<TOut, PRECISE, true, true, NH>(xw, acc, cur, vlast, coef, e, 0, yp, row_bytes, ydelta);
                 } else {
-                    act1d_nlc_body<TOut, PRECISE, true, false>(xw, acc, cur, vlast, coef, e, g0, yp, row_bytes);
+                    act1d_nlc_body<TOut, PRECISE, true, false, NH>(xw, acc, cur, vlast, coef, e, g0, yp, row_bytes, ydelta);
                 }
             } else {
                 if (body == 0)
-                    act1d_nlc_body<TOut, PRECISE, false, true>(xw, acc, cur, vlast, coef, e, 0, yp, row_bytes);
+                    act1d_nlc_body<TOut, PRECISE, false, true, NH>(xw, acc, cur, vlast, coef, e, 0, yp, row_bytes, ydelta);
                 else
-                    act1d_nlc_body<TOut, PRECISE, false, false>(xw, acc, cur, vlast, coef, e, g0, yp, row_bytes);
+                    act1d_nlc_body<TOut, PRECISE, false, false, NH>(xw, acc, cur, vlast, coef, e, g0, yp, row_bytes, ydelta);
             }
         }
     }
@@ -691,9 +720,9 @@ static int launch_nlc(const void* x, void* y, const float* alpha, const float* b
 
 // TMA-pipelined launcher.  Returns BVG_OK after launching, or a positive value when the shape does not suit the TMA
 // path (C not a multiple of 8, ...) and the caller should use the direct-load kernel.
-template <typename TIn, typename TOut>
-static int launch_nlc_tma(const void* x, void* y, const float* alpha, const float* beta, int64_t B, int64_t T, int64_t C,
-                          int precise, cudaStream_t st) {
+template <typename TIn, typename TOut, int NH>
+static int launch_nlc_tma(const void* x, const ActHeads<NH>& hd, int64_t B, int64_t T, int64_t C, int precise,
+                          cudaStream_t st) {
     if (C % 8 != 0 || T >= (int64_t(1) << 31) - 4096 || reinterpret_cast<uintptr_t>(x) % 16 != 0) return 1;
     ActTmaParams p{};
     p.T = T;
@@ -711,7 +740,7 @@ static int launch_nlc_tma(const void* x, void* y, const float* alpha, const floa
     // persistent grid (favour many short units).  Ties go to the longer segment.
     int L = 8;
     {
-        const int64_t ctas = (int64_t)ACT_TMA_MIN_CTAS * sms;
+        const int64_t ctas = (int64_t)act_tma_min_ctas(NH) * sms;
         int64_t best = -1;
         for (int cand = 120; cand >= 8; cand -= 7) {
             const int64_t units_c = B * ceil_div(T, (int64_t)p.nsegs * cand) * p.n_cchunks;
@@ -771,12 +800,13 @@ static int launch_nlc_tma(const void* x, void* y, const float* alpha, const floa
                      CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     BVG_REQUIRE(r == CUDA_SUCCESS, BVG_ERR_CUDA, "cuTensorMapEncodeTiled(activation input) failed with CUresult %d", (int)r);
 
-    auto kern = precise ? act1d_nlc_tma_kernel<TIn, TOut, true> : act1d_nlc_tma_kernel<TIn, TOut, false>;
+    auto kern = precise ? act1d_nlc_tma_kernel<TIn, TOut, true, NH> : act1d_nlc_tma_kernel<TIn, TOut, false, NH>;
     BVG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024));
     // same L1/shared split as the conv kernel: CTAs of the two kernels can then be resident on one SM at the same time
     BVG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     static const int grid_mode = []() { const char* e = getenv("BVG_ACT_GRID"); return e ? atoi(e) : 0; }();
-    int grid = static_cast<int>(units < (long long)ACT_TMA_MIN_CTAS * sms ? units : (long long)ACT_TMA_MIN_CTAS * sms);
+    const long long max_ctas = (long long)act_tma_min_ctas(NH) * sms;
+    int grid = static_cast<int>(units < max_ctas ? units : max_ctas);
     if (grid_mode == 1) grid = static_cast<int>(units);                      // one unit per CTA: hardware load balancing
     if (grid_mode == 2) grid = static_cast<int>(units < sms ? units : sms);  // one CTA per SM
     {
@@ -790,7 +820,7 @@ static int launch_nlc_tma(const void* x, void* y, const float* alpha, const floa
         attr[0].val.programmaticStreamSerializationAllowed = 1;
         cfg.attrs = attr;
         cfg.numAttrs = pdl_enabled() ? 1 : 0;
-        BVG_CUDA(cudaLaunchKernelEx(&cfg, kern, map, static_cast<TOut*>(y), alpha, beta, p));
+        BVG_CUDA(cudaLaunchKernelEx(&cfg, kern, map, hd, p));
     }
     BVG_LAUNCH_CHECK("act1d_nlc_tma_kernel");
     return BVG_OK;
@@ -808,7 +838,11 @@ template <typename TIn, typename TOut>
 static int launch_nlc_any(const void* x, void* y, const float* alpha, const float* beta, int64_t B, int64_t T, int64_t C,
                           int precise, cudaStream_t st) {
     if (!act_legacy_requested()) {
-        const int rc = launch_nlc_tma<TIn, TOut>(x, y, alpha, beta, B, T, C, precise, st);
+        ActHeads<1> hd;
+        hd.y[0] = y;
+        hd.alpha[0] = alpha;
+        hd.beta[0] = beta;
+        const int rc = launch_nlc_tma<TIn, TOut, 1>(x, hd, B, T, C, precise, st);
         if (rc <= 0) return rc;
     }
     return launch_nlc<TIn, TOut>(x, y, alpha, beta, B, T, C, precise, st);
@@ -830,6 +864,58 @@ int activation1d_nlc(const void* x, int x_dtype, void* y, int y_dtype, const flo
     if (x_dtype == BVG_BF16 && y_dtype == BVG_F32)
         return launch_nlc_any<__nv_bfloat16, float>(x, y, alpha, beta, B, T, C, precise, st);
     return set_error(BVG_ERR_UNSUPPORTED, "activation1d_nlc: unsupported dtypes %d -> %d", x_dtype, y_dtype);
+}
+
+// Three Activation1d of the same tensor (the first activations of the three AMP blocks of a stage) in one launch; falls
+// back to three launches for shapes the TMA kernel does not take.
+template <typename TIn, typename TOut>
+static int launch_nlc_heads3(const void* x, void* const* ys, const float* const* alphas, const float* const* betas, int64_t B,
+                             int64_t T, int64_t C, int precise, cudaStream_t st) {
+    if (!act_legacy_requested()) {
+        ActHeads<3> hd;
+        for (int h = 0; h < 3; ++h) {
+            hd.y[h] = ys[h];
+            hd.alpha[h] = alphas[h];
+            hd.beta[h] = betas[h];
+        }
+        const int rc = launch_nlc_tma<TIn, TOut, 3>(x, hd, B, T, C, precise, st);
+        if (rc <= 0) return rc;
+    }
+    for (int h = 0; h < 3; ++h) {
+        const int rc = launch_nlc_any<TIn, TOut>(x, ys[h], alphas[h], betas[h], B, T, C, precise, st);
+        if (rc != BVG_OK) return rc;
+    }
+    return BVG_OK;
+}
+
+int activation1d_nlc_multi(const void* x, int x_dtype, void* const* ys, int y_dtype, const float* const* alphas,
+                           const float* const* betas, int n_heads, int64_t B, int64_t T, int64_t C, int precise,
+                           cudaStream_t st) {
+    BVG_REQUIRE(x && ys && alphas && betas && n_heads >= 1 && n_heads <= 8, BVG_ERR_INVALID,
+                "activation1d_nlc_multi: null pointer or bad head count %d", n_heads);
+    for (int h = 0; h < n_heads; ++h) {
+        BVG_REQUIRE(ys[h] && alphas[h] && betas[h], BVG_ERR_INVALID, "activation1d_nlc_multi: null pointer (head %d)", h);
+        BVG_REQUIRE(ys[h] != x, BVG_ERR_INVALID, "activation1d_nlc_multi: in-place is not supported");
+    }
+    BVG_REQUIRE(B >= 0 && T >= 0 && C > 0 && C % 2 == 0 && B <= 65535, BVG_ERR_INVALID,
+                "activation1d_nlc_multi: bad shape B=%lld T=%lld C=%lld", (long long)B, (long long)T, (long long)C);
+    if (B == 0 || T == 0) return BVG_OK;
+    int h0 = 0;
+    for (; h0 + 3 <= n_heads; h0 += 3) {
+        int rc;
+        if (x_dtype == BVG_F32 && y_dtype == BVG_BF16)
+            rc = launch_nlc_heads3<float, __nv_bfloat16>(x, ys + h0, alphas + h0, betas + h0, B, T, C, precise, st);
+        else if (x_dtype == BVG_F32 && y_dtype == BVG_F32)
+            rc = launch_nlc_heads3<float, float>(x, ys + h0, alphas + h0, betas + h0, B, T, C, precise, st);
+        else
+            break;  // bf16-input combinations: no fused instantiation, one launch per head below
+        if (rc != BVG_OK) return rc;
+    }
+    for (int h = h0; h < n_heads; ++h) {
+        const int rc = activation1d_nlc(x, x_dtype, ys[h], y_dtype, alphas[h], betas[h], B, T, C, precise, st);
+        if (rc != BVG_OK) return rc;
+    }
+    return BVG_OK;
 }
 
 template <typename TIO>
@@ -875,4 +961,11 @@ extern "C" int bvg_activation1d_nlc_fwd(const void* x, int x_dtype, void* y, int
                                         void* stream) {
     return activation1d_nlc(x, x_dtype, y, y_dtype, alpha_log, beta_log, B, T, C, precise,
                             static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int bvg_activation1d_nlc_multi_fwd(const void* x, int x_dtype, void* const* ys, int y_dtype,
+                                              const float* const* alphas_log, const float* const* betas_log, int n_heads,
+                                              int64_t B, int64_t T, int64_t C, int precise, void* stream) {
+    return activation1d_nlc_multi(x, x_dtype, ys, y_dtype, alphas_log, betas_log, n_heads, B, T, C, precise,
+                                  static_cast<cudaStream_t>(stream));
 }

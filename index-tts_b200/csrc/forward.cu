@@ -13,6 +13,9 @@ int conv_simt_launch(const void* x, const void* w_packed, const float* bias, con
                      int taps, int dil, const int* tap_base, int num_phases, float out_scale, cudaStream_t st);
 int activation1d_nlc(const void* x, int x_dtype, void* y, int y_dtype, const float* alpha, const float* beta,
                      int64_t B, int64_t T, int64_t C, int precise, cudaStream_t st);
+int activation1d_nlc_multi(const void* x, int x_dtype, void* const* ys, int y_dtype, const float* const* alphas,
+                           const float* const* betas, int n_heads, int64_t B, int64_t T, int64_t C, int precise,
+                           cudaStream_t st);
 int transpose_any(const void* src, int src_dtype, void* dst, int dst_dtype, int64_t B, int64_t R, int64_t Cc, int64_t sb,
                   int64_t sr, cudaStream_t st);
 
@@ -165,6 +168,15 @@ static AuxStreams* aux_streams() {
     return good ? &a : nullptr;
 }
 
+// BVG_ACT_MULTI=0: one Activation1d launch per AMP block at the top of a stage instead of the shared-up-sampler kernel
+static int act_multi_requested() {
+    static const int v = []() {
+        const char* e = getenv("BVG_ACT_MULTI");
+        return (e != nullptr && e[0] == '0' && e[1] == 0) ? 0 : 1;
+    }();
+    return v;
+}
+
 static int concurrency_requested() {
     static const int v = []() {
         const char* e = getenv("BVG_STREAMS");
@@ -263,6 +275,25 @@ static int forward_impl(const bvg_model_desc* m, const float* mel, int64_t mel_s
         T *= u;
         C /= 2;
         const bool last_stage = (i + 1 == m->num_stages);
+        // The AMP blocks all begin with an Activation1d of X (bigvgan.py:133-135): one launch computes the 2x up-sampling
+        // of X once and applies the blocks' snake parameters to it (activation1d_nlc_multi), before the streams fork.
+        const bool heads = act_multi_requested() && m->num_kernels == 3 && m->num_dilations >= 1;
+        if (heads) {
+            void* ys[BVG_MAX_KERNELS];
+            const float* als[BVG_MAX_KERNELS];
+            const float* bes[BVG_MAX_KERNELS];
+            for (int j = 0; j < m->num_kernels; ++j) {
+                ys[j] = ws + pl.off_a[j];
+                als[j] = m->acts[i][j][0].alpha_log;
+                bes[j] = m->acts[i][j][0].beta_log;
+            }
+            const double rows = (double)B * T;
+            // algorithmic work = the sum of the three reference layers this launch implements
+            ProfScope ps(BVG_K_ACT, i, C, C, 0, 0, B * T, m->num_kernels * 62.0 * rows * C,
+                         m->num_kernels * (2.0 * es * rows * C + 8.0 * C), st);
+            rc = activation1d_nlc_multi(X, BVG_F32, ys, op_dt, als, bes, m->num_kernels, B, T, C, precise, st);
+            if (rc != BVG_OK) return rc;
+        }
         if (aux) {
             BVG_CUDA(cudaEventRecord(aux->fork, st));
             for (int j = 1; j < m->num_kernels; ++j) BVG_CUDA(cudaStreamWaitEvent(aux->s[j - 1], aux->fork, 0));
@@ -280,7 +311,7 @@ static int forward_impl(const bvg_model_desc* m, const float* mel, int64_t mel_s
                 const bvg_act_desc& a2 = m->acts[i][j][2 * l + 1];
                 const double rows = (double)B * T;
                 const double act_flops = 62.0 * rows * C, act_bytes = 2.0 * es * rows * C + 8.0 * C;
-                {
+                if (!(heads && l == 0)) {
                     ProfScope ps(BVG_K_ACT, i, C, C, 0, 0, B * T, act_flops, act_bytes, sj);
                     rc = activation1d_nlc(xr, BVG_F32, A, op_dt, a1.alpha_log, a1.beta_log, B, T, C, precise, sj);
                 }

@@ -97,6 +97,26 @@ def activation1d_nlc(x: torch.Tensor, alpha_log: torch.Tensor, beta_log: torch.T
     return y
 
 
+def activation1d_nlc_multi(x: torch.Tensor, alphas_log, betas_log, out_dtype: torch.dtype, precise: bool):
+    """``[Activation1d(x; alphas_log[h], betas_log[h]) for h]`` on a channels-last ``[B, T, C]`` tensor: the first
+    activations of the AMP blocks of one stage (bigvgan.py:369-374, :133-135) share their up-sampler in one launch."""
+    import ctypes
+    _require_cuda(x, "activation1d_nlc_multi")
+    x = x.contiguous()
+    B, T, C = x.shape
+    n = len(alphas_log)
+    if n == 0 or len(betas_log) != n:
+        raise _lib.BvgError("activation1d_nlc_multi: need as many beta as alpha tensors (at least one)")
+    ys = [torch.empty((B, T, C), dtype=out_dtype, device=x.device) for _ in range(n)]
+    arr = ctypes.c_void_p * n
+    with torch.cuda.device(x.device):
+        check(_lib.load().bvg_activation1d_nlc_multi_fwd(
+            x.data_ptr(), _dt(x, "activation1d_nlc_multi"), arr(*[y.data_ptr() for y in ys]), _DT[out_dtype],
+            arr(*[a.data_ptr() for a in alphas_log]), arr(*[b.data_ptr() for b in betas_log]), n, B, T, C,
+            int(bool(precise)), _stream()), "bvg_activation1d_nlc_multi_fwd")
+    return ys
+
+
 # ---------------------------------------------------------------------------------------------------------------
 # layout + weights
 # ---------------------------------------------------------------------------------------------------------------

@@ -115,6 +115,36 @@ def test_activation1d_nlc_bf16_out_long(ops, in_dtype):
     assert rel_err(ref, y) < 2.0 ** -7 and snr_db(ref, y) > 45
 
 
+@pytest.mark.parametrize("C,T", [(24, 1), (24, 7), (48, 333), (96, 1000), (384, 130), (768, 64), (24, 50001), (10, 40)])
+@pytest.mark.parametrize("out_dtype,precise", [(torch.float32, True), (torch.bfloat16, False)])
+def test_activation1d_nlc_multi_equals_single_calls(ops, C, T, out_dtype, precise):
+    """The shared-up-sampler launch (first activations of the three AMP blocks of a stage) must equal three plain calls
+    bit for bit -- every stage width, edge-only / edge + interior lengths, both arithmetic modes; C = 10 takes the
+    non-TMA fallback; 1, 2, 4 and 6 heads exercise the grouping; bf16 input has no fused instantiation."""
+    rng = np.random.default_rng(C * 7 + T)
+    B = 2
+    x = _t((rng.standard_normal((B, T, C)) * 1.5).astype(np.float32))
+    als = [_t((0.5 * rng.standard_normal(C)).astype(np.float32)) for _ in range(6)]
+    bes = [_t((0.5 * rng.standard_normal(C)).astype(np.float32)) for _ in range(6)]
+    singles = [ops.activation1d_nlc(x, a, b, out_dtype, precise) for a, b in zip(als, bes)]
+    for n in (3, 1, 2, 4, 6):
+        ys = ops.activation1d_nlc_multi(x, als[:n], bes[:n], out_dtype, precise)
+        assert len(ys) == n
+        for h in range(n):
+            assert ys[h].dtype == out_dtype and torch.equal(ys[h], singles[h]), (n, h)
+    # the oracle, once (the single-call kernel is pinned to it elsewhere; this pins the fused path directly)
+    ref = O.activation1d(np.transpose(x.cpu().numpy(), (0, 2, 1)).astype(np.float64), als[2].cpu().numpy(), bes[2].cpu().numpy())
+    got = np.transpose(ops.activation1d_nlc_multi(x, als[:3], bes[:3], out_dtype, precise)[2].float().cpu().numpy(), (0, 2, 1))
+    if out_dtype == torch.float32:
+        np.testing.assert_allclose(got, ref, rtol=0, atol=2e-5)
+    else:
+        assert rel_err(ref, got) < 2.0 ** -7
+    xb = x.bfloat16()
+    ys = ops.activation1d_nlc_multi(xb, als[:3], bes[:3], torch.bfloat16, False)
+    for h in range(3):
+        assert torch.equal(ys[h], ops.activation1d_nlc(xb, als[h], bes[h], torch.bfloat16, False))
+
+
 # ---------------------------------------------------------------------------------------------------------------
 # layout + weight preparation
 # ---------------------------------------------------------------------------------------------------------------
