@@ -254,9 +254,10 @@ def fold_conv1d_weight(w: torch.Tensor, dilation: int, fold: int) -> torch.Tenso
     return out
 
 
-# Fold AMP-block convs of stages with at most this many channels by FOLD_FACTOR (stages up to 48 channels by 2: measured
-# -10 % on their k = 7 layers, neutral elsewhere) when the folded conv needs at most FOLD_MAX_TAPS taps (the folded GEMM does fold*taps'/k times the FLOPs on an otherwise idle tensor pipe; beyond ~5 taps
-# the weights stop being shared-memory resident and the layer gets slower instead).  BVG_FOLD=0 switches it off.
+# Time folding of the AMP-block convs of small-channel stages (include/bvg.h, bvg_conv_desc::fold): stages with at most
+# FOLD_MAX_CHANNELS channels are folded by FOLD_FACTOR (C = 24 -> 96), wider ones up to C = 64 by 2 (C = 48 -> 96), when
+# the folded conv stays within _fold_max_taps() taps.  The folded GEMM does fold*taps'/k times the FLOPs on an otherwise
+# idle tensor pipe and gets 4x / 2x fewer, wider tiles in exchange.  BVG_FOLD=0 switches it off.
 FOLD_MAX_CHANNELS = 32
 FOLD_FACTOR = 4
 FOLD_MAX_TAPS = 5

@@ -14,8 +14,9 @@ cat "${OUT}/layers_isolated.log"
 if [ "${SKIP_NCU:-0}" != "1" ]; then
   CMD="python bench.py --steps 1 --warmup 3 --no-cpu-baseline"
   timeout 300 $CMD > "${OUT}/plain.log" 2>&1 &&
-  timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -s 693 -c 231 --csv --log-file "${OUT}/launches.csv" $CMD > "${OUT}/ncu_launches.log" 2>&1
+  timeout 700 ncu --metrics gpu__time_duration.sum --clock-control none -c 1800 --csv --log-file "${OUT}/launches_all.csv" $CMD > "${OUT}/ncu_launches.log" 2>&1
   echo "ncu launches rc=$?"
+  python tools/launch_share.py "${OUT}/launches_all.csv" "${OUT}/launches.csv" > "${OUT}/launches_summary.txt"; cat "${OUT}/launches_summary.txt"
   C1="python tools/run_one.py conv 384 13792 11 1 0"
   timeout 120 $C1 > "${OUT}/plain_conv.log" 2>&1 &&
   timeout 600 ncu --set full --clock-control none --import-source on -k regex:conv_umma -s 2 -c 1 -f -o "${OUT}/prof_conv_c384k11" $C1 > "${OUT}/ncu_conv.log" 2>&1
