@@ -179,6 +179,10 @@ typedef struct {
     int32_t upsample_kernel_sizes[BVG_MAX_STAGES];
     int32_t use_tanh_at_final;
     int32_t precision;                          /* bvg_precision */
+    int32_t resblock;                           /* 1 (or 0) = AMPBlock1: act, convs1[l], act, convs2[l], +x per dilation
+                                                 * (BV/bigvgan.py:132-141); 2 = AMPBlock2: act, convs1[l], +x (:231-236 of
+                                                 * indextts/BigVGAN/bigvgan.py; convs2 and acts[..][l >= num_dilations]
+                                                 * unused).  Occupies what used to be struct padding. */
     bvg_conv_desc conv_pre;
     bvg_conv_desc ups[BVG_MAX_STAGES];          /* k = transposed-conv kernel size K, dilation unused */
     bvg_conv_desc convs1[BVG_MAX_STAGES][BVG_MAX_KERNELS][BVG_MAX_DILATIONS];
@@ -202,12 +206,37 @@ BVG_API int bvg_forward_pcm16(const bvg_model_desc* m_host, const float* mel, in
                       int16_t* pcm, int64_t B, int64_t T_mel, void* workspace, size_t workspace_bytes, void* stream);
 
 /* ---------------------------------------------------------------------------------------------------------- */
+/* v1 generator (indextts/BigVGAN/models.py:130-258 BigVGAN.forward after the speaker encoder): the same stack with a
+ * per-utterance conditioning vector added after conv_pre (:236) and after every transposed conv (:244-245), and a
+ * channels-last input (the GPT latent [B, T, gpt_dim], :231 `x.transpose(1, 2)`).                               */
+
+/* y[b, :] = w[C, D] . e[b, :] + bias: cond_layer / conds[i], a 1x1 Conv1d applied to the length-1 speaker embedding
+ * (models.py:197-202).  e: fp32 [B, D]; w: fp32 [C, D] (the module's [C, D, 1] weight); bias [C] or NULL; y: fp32 [B, C]. */
+BVG_API int bvg_cond_linear_fwd(const float* e, const float* w, const float* bias, float* y, int64_t B, int64_t D, int64_t C,
+                        void* stream);
+
+/* y[b, t, c] = x[b, t, c] + v[b, c] (nlc, dense; v fp32 [B, C] or NULL = dtype conversion only; x may alias y when the
+ * dtypes match).  C % 4 == 0. */
+BVG_API int bvg_add_channel_vector_nlc(const void* x, int x_dtype, const float* v, void* y, int y_dtype, int64_t B, int64_t T,
+                               int64_t C, void* stream);
+
+/* bvg_forward for the v1 generator.  x: fp32, either ncl [B, num_mels, T] with element strides (x_stride_b, x_stride_c, 1)
+ * (x_layout = 0, exactly bvg_forward's input) or dense nlc [B, T, num_mels] (x_layout = 1; strides ignored).
+ * cond_host: HOST array of num_stages + 1 device pointers (or NULL = no conditioning at all): cond_host[0] is the fp32
+ * [B, upsample_initial_channel] vector added to conv_pre's output, cond_host[i + 1] the [B, C_i] vector added to
+ * ups[i]'s output; NULL entries are skipped (models.py:244 `cond_in_each_up_layer` false).  m_host->num_mels is conv_pre's
+ * input width (gpt_dim for the v1 model). */
+BVG_API int bvg_forward_cond(const bvg_model_desc* m_host, const float* x, int x_layout, int64_t x_stride_b, int64_t x_stride_c,
+                     const float* const* cond_host, float* wav, int64_t B, int64_t T, void* workspace,
+                     size_t workspace_bytes, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------------- */
 /* measurement: the same launch plan as bvg_forward with a CUDA event pair around every kernel launch (recorded on
  * `stream`).  Synchronises `stream` before returning -- a profiling entry point, not a product path.  Fills up to
  * max_records host records in launch order; *n_records = number of launches.  flops / bytes are the ALGORITHMIC
  * work of the reference layer the launch implements (bf16 IO element size in BVG_BF16_TC mode,
  * fp32 in BVG_EXACT_F32 mode; intermediates at the 2x rate and padding are not counted).                        */
-typedef enum { BVG_K_LAYOUT = 0, BVG_K_CONV1D = 1, BVG_K_CONVT = 2, BVG_K_ACT = 3, BVG_K_POST = 4 } bvg_launch_kind;
+typedef enum { BVG_K_LAYOUT = 0, BVG_K_CONV1D = 1, BVG_K_CONVT = 2, BVG_K_ACT = 3, BVG_K_POST = 4, BVG_K_COND = 5 } bvg_launch_kind;
 typedef struct {
     int32_t kind;          /* bvg_launch_kind */
     int32_t stage;         /* -1 = pre / post, else upsample stage */

@@ -40,6 +40,7 @@ class ModelDesc(C.Structure):
         ("upsample_kernel_sizes", C.c_int32 * MAX_STAGES),
         ("use_tanh_at_final", C.c_int32),
         ("precision", C.c_int32),
+        ("resblock", C.c_int32),
         ("conv_pre", ConvDesc),
         ("ups", ConvDesc * MAX_STAGES),
         ("convs1", ((ConvDesc * MAX_DILATIONS) * MAX_KERNELS) * MAX_STAGES),
@@ -56,7 +57,7 @@ class LaunchRecord(C.Structure):
                 ("ms", C.c_float)]
 
 
-KIND_NAMES = {0: "layout", 1: "conv1d", 2: "convtranspose1d", 3: "activation1d", 4: "conv_post"}
+KIND_NAMES = {0: "layout", 1: "conv1d", 2: "convtranspose1d", 3: "activation1d", 4: "conv_post", 5: "cond_add"}
 
 # name -> (restype, argtypes); must list every symbol include/bvg.h declares (tests/test_abi.py checks that)
 SIGNATURES = {
@@ -86,6 +87,10 @@ SIGNATURES = {
     "bvg_forward_profile": (c_int, [C.POINTER(ModelDesc), c_vp, c_i64, c_i64, c_vp, c_i64, c_i64, c_vp, c_sz, c_vp,
                                     C.POINTER(LaunchRecord), c_int, C.POINTER(c_int)]),
     "bvg_debug_conv_trace": (None, [c_vp, c_int]),
+    "bvg_cond_linear_fwd": (c_int, [c_vp, c_vp, c_vp, c_vp, c_i64, c_i64, c_i64, c_vp]),
+    "bvg_add_channel_vector_nlc": (c_int, [c_vp, c_int, c_vp, c_vp, c_int, c_i64, c_i64, c_i64, c_vp]),
+    "bvg_forward_cond": (c_int, [C.POINTER(ModelDesc), c_vp, c_int, c_i64, c_i64, C.POINTER(c_vp), c_vp, c_i64, c_i64,
+                                 c_vp, c_sz, c_vp]),
 }
 
 _lock = threading.Lock()

@@ -18,7 +18,7 @@ import json
 import os
 import weakref
 from pathlib import Path
-from typing import Dict, Optional, Union
+from typing import Dict, List, Optional, Union
 
 import torch
 import torch.nn as nn
@@ -284,14 +284,15 @@ class _PackedGenerator:
         for u in h.upsample_rates:
             self.hop *= int(u)
         d = _lib.ModelDesc()
-        d.num_mels = int(h.num_mels)
+        d.num_mels = int(model.conv_pre.in_channels)  # h.num_mels here; h.gpt_dim for the v1 generator (v1.py)
         d.upsample_initial_channel = int(h.upsample_initial_channel)
         d.num_stages = model.num_upsamples
         d.num_kernels = model.num_kernels
-        dil = h.resblock_dilation_sizes
-        if len({len(x) for x in dil}) != 1:
+        # dilations per AMP block, read off the modules (the v1 AMPBlock2 keeps two whatever the config lists, v1.py)
+        dil = {len(rb.convs if isinstance(rb, AMPBlock2) else rb.convs1) for rb in model.resblocks}
+        if len(dil) != 1:
             raise NotImplementedError("resblock_dilation_sizes must have the same length for every kernel size")
-        d.num_dilations = len(dil[0])
+        d.num_dilations = dil.pop()
         if d.num_stages > _lib.MAX_STAGES or d.num_kernels > _lib.MAX_KERNELS or d.num_dilations > _lib.MAX_DILATIONS:
             raise NotImplementedError("generator larger than the libbvg descriptor limits")
         for i, (u, k) in enumerate(zip(h.upsample_rates, h.upsample_kernel_sizes)):
@@ -343,14 +344,20 @@ class _PackedGenerator:
             time_factor *= int(h.upsample_rates[i])
             for j in range(model.num_kernels):
                 rb = model.resblocks[i * model.num_kernels + j]
-                if not isinstance(rb, AMPBlock1):
-                    raise NotImplementedError("the fused generator plan implements resblock '1' (AMPBlock1); "
-                                              "AMPBlock2 is available as a standalone module only")
-                for l in range(d.num_dilations):
-                    conv(d.convs1[i][j][l], rb.convs1[l], time_factor=time_factor)
-                    conv(d.convs2[i][j][l], rb.convs2[l], time_factor=time_factor)
-                for a in range(2 * d.num_dilations):
-                    act(d.acts[i][j][a], rb.activations[a])
+                kind = 2 if isinstance(rb, AMPBlock2) else (1 if isinstance(rb, AMPBlock1) else 0)
+                if kind == 0 or d.resblock not in (0, kind):
+                    raise NotImplementedError("the fused generator plan needs all resblocks to be AMPBlock1 or all AMPBlock2")
+                d.resblock = kind
+                if kind == 1:
+                    for l in range(d.num_dilations):
+                        conv(d.convs1[i][j][l], rb.convs1[l], time_factor=time_factor)
+                        conv(d.convs2[i][j][l], rb.convs2[l], time_factor=time_factor)
+                    for a in range(2 * d.num_dilations):
+                        act(d.acts[i][j][a], rb.activations[a])
+                else:  # AMPBlock2: one conv and one activation per dilation (bvg.h, bvg_model_desc::resblock)
+                    for l in range(d.num_dilations):
+                        conv(d.convs1[i][j][l], rb.convs[l], time_factor=time_factor)
+                        act(d.acts[i][j][l], rb.activations[l])
         act(d.act_post, model.activation_post)
         cp = model.conv_post
         w_post = f32(_effective_weight(cp))
@@ -362,6 +369,30 @@ class _PackedGenerator:
         self.plan_id = _next_plan_id[0]
         _next_plan_id[0] += 1
         _PLANS[self.plan_id] = self
+
+    def run_cond(self, x_nlc: torch.Tensor, conds) -> torch.Tensor:
+        """v1 generator (v1.py): ``x_nlc`` fp32 ``[B, T, gpt_dim]``, ``conds`` = ``num_stages + 1`` fp32 ``[B, C_i]``
+        tensors (or ``None`` entries) added after ``conv_pre`` / each transposed conv (``bvg_forward_cond``)."""
+        lib = _lib.load()
+        B, T, _ = x_nlc.shape
+        wav = torch.empty((B, 1, T * self.hop), dtype=torch.float32, device=x_nlc.device)
+        if B == 0 or T == 0:
+            return wav
+        x_nlc = x_nlc.contiguous()
+        n = self.desc.num_stages + 1
+        if len(conds) != n:
+            raise _lib.BvgError(f"run_cond: expected {n} conditioning vectors, got {len(conds)}")
+        conds = [None if c is None else c.detach().to(device=x_nlc.device, dtype=torch.float32).contiguous() for c in conds]
+        arr = (ctypes.c_void_p * n)(*[None if c is None else c.data_ptr() for c in conds])
+        ws_bytes = lib.bvg_workspace_bytes(ctypes.byref(self.desc), B, T)
+        if ws_bytes == 0:
+            _lib.check(-1, "bvg_workspace_bytes")
+        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=x_nlc.device)
+        with torch.cuda.device(x_nlc.device):
+            _lib.check(lib.bvg_forward_cond(ctypes.byref(self.desc), x_nlc.data_ptr(), 1, 0, 0, arr, wav.data_ptr(), B, T,
+                                            ws.data_ptr(), ws_bytes, torch.cuda.current_stream().cuda_stream),
+                       "bvg_forward_cond")
+        return wav
 
     def run(self, mel: torch.Tensor, pcm16: bool = False) -> torch.Tensor:
         lib = _lib.load()
@@ -421,6 +452,19 @@ def _(mel, plan_id, hop):
     return mel.new_empty((mel.shape[0], 1, mel.shape[2] * hop), dtype=torch.float32)
 
 
+@torch.library.custom_op("bvg::vocoder_forward_cond", mutates_args=())
+def _vocoder_forward_cond(x_nlc: torch.Tensor, conds: List[torch.Tensor], plan_id: int, hop: int) -> torch.Tensor:
+    plan = _PLANS.get(plan_id)
+    if plan is None:
+        raise _lib.BvgError(f"bvg::vocoder_forward_cond: plan {plan_id} no longer exists")
+    return plan.run_cond(x_nlc, [None if c.numel() == 0 else c for c in conds])
+
+
+@_vocoder_forward_cond.register_fake
+def _(x_nlc, conds, plan_id, hop):
+    return x_nlc.new_empty((x_nlc.shape[0], 1, x_nlc.shape[1] * hop), dtype=torch.float32)
+
+
 @torch.library.custom_op("bvg::vocoder_forward_pcm16", mutates_args=())
 def _vocoder_forward_pcm16(mel: torch.Tensor, plan_id: int, hop: int) -> torch.Tensor:
     plan = _PLANS.get(plan_id)
@@ -434,7 +478,42 @@ def _(mel, plan_id, hop):
     return mel.new_empty((mel.shape[0], 1, mel.shape[2] * hop), dtype=torch.int16)
 
 
+class _GeneratorPlanMixin:
+    """Precision switch and the cached whole-generator launch plan, shared by the v2 ``BigVGAN`` below and the v1
+    generator (``v1.py``).  Expects ``self.__dict__['_bvg_precision' | '_bvg_plan' | '_bvg_plan_key']``."""
+
+    def _init_plan_state(self):
+        self.__dict__["_bvg_precision"] = DEFAULT_PRECISION
+        self.__dict__["_bvg_plan"] = None
+        self.__dict__["_bvg_plan_key"] = None
+
+    def set_precision(self, precision: str):
+        ops.precision_code(precision)
+        self.__dict__["_bvg_precision"] = precision
+        for m in self.modules():
+            if isinstance(m, (Conv1d, ConvTranspose1d, AMPBlock1, AMPBlock2)):
+                m.bvg_precision = precision
+        return self
+
+    @property
+    def precision(self) -> str:
+        return self.__dict__["_bvg_precision"]
+
+    def _plan(self, device: torch.device) -> _PackedGenerator:
+        prec = ops.precision_code(self.__dict__["_bvg_precision"])
+        key = (device, prec, tuple((p.data_ptr(), p._version) for p in self.parameters()))
+        if self.__dict__["_bvg_plan"] is None or self.__dict__["_bvg_plan_key"] != key:
+            for p in self.parameters():
+                if p.device != device:
+                    raise _lib.BvgError(f"generator parameters live on {p.device} but the input is on {device}; "
+                                        "call .to(device) first")
+            self.__dict__["_bvg_plan"] = _PackedGenerator(self, device, prec)
+            self.__dict__["_bvg_plan_key"] = key
+        return self.__dict__["_bvg_plan"]
+
+
 class BigVGAN(
+    _GeneratorPlanMixin,
     torch.nn.Module,
     PyTorchModelHubMixin,
     library_name="bigvgan",
@@ -502,34 +581,7 @@ class BigVGAN(
         self.conv_post.apply(init_weights)
 
         self.use_tanh_at_final = h.get("use_tanh_at_final", True)
-        self.__dict__["_bvg_precision"] = DEFAULT_PRECISION
-        self.__dict__["_bvg_plan"] = None
-        self.__dict__["_bvg_plan_key"] = None
-
-    # ---- libbvg plumbing ---------------------------------------------------------------------------------
-    def set_precision(self, precision: str) -> "BigVGAN":
-        ops.precision_code(precision)
-        self.__dict__["_bvg_precision"] = precision
-        for m in self.modules():
-            if isinstance(m, (Conv1d, ConvTranspose1d, AMPBlock1, AMPBlock2)):
-                m.bvg_precision = precision
-        return self
-
-    @property
-    def precision(self) -> str:
-        return self.__dict__["_bvg_precision"]
-
-    def _plan(self, device: torch.device) -> _PackedGenerator:
-        prec = ops.precision_code(self.__dict__["_bvg_precision"])
-        key = (device, prec, tuple((p.data_ptr(), p._version) for p in self.parameters()))
-        if self.__dict__["_bvg_plan"] is None or self.__dict__["_bvg_plan_key"] != key:
-            for p in self.parameters():
-                if p.device != device:
-                    raise _lib.BvgError(f"BigVGAN parameters live on {p.device} but the input is on {device}; "
-                                        "call .to(device) first")
-            self.__dict__["_bvg_plan"] = _PackedGenerator(self, device, prec)
-            self.__dict__["_bvg_plan_key"] = key
-        return self.__dict__["_bvg_plan"]
+        self._init_plan_state()
 
     def forward(self, x):
         """``[B, num_mels, T_mel]`` CUDA tensor -> ``[B, 1, T_mel * hop]`` fp32 in [-1, 1] (reference :360-386)."""

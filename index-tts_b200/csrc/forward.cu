@@ -18,6 +18,8 @@ int activation1d_nlc_multi(const void* x, int x_dtype, void* const* ys, int y_dt
                            cudaStream_t st);
 int transpose_any(const void* src, int src_dtype, void* dst, int dst_dtype, int64_t B, int64_t R, int64_t Cc, int64_t sb,
                   int64_t sr, cudaStream_t st);
+int add_channel_vector(const void* x, int x_dtype, const float* v, void* y, int y_dtype, int64_t B, int64_t T, int64_t C,
+                       cudaStream_t st);
 
 static int conv_dispatch(int precision, const void* x, const void* w, const float* bias, const float* residual,
                          const float* accum, float* y_f32, void* y_bf16, int64_t B, int64_t T, int64_t Cin, int64_t N,
@@ -116,7 +118,9 @@ static int make_plan(const bvg_model_desc* m, int64_t B, int64_t T_mel, Plan* pl
     pl->B = B;
     pl->T_mel = T_mel;
     pl->op_es = m->precision == BVG_BF16_TC ? 2 : 4;
-    int64_t T = T_mel, E = 0;
+    BVG_REQUIRE(m->resblock >= 0 && m->resblock <= 2, BVG_ERR_UNSUPPORTED, "model descriptor: unknown resblock type %d",
+                m->resblock);
+    int64_t T = T_mel, E = B * T_mel * m->upsample_initial_channel;
     for (int i = 0; i < m->num_stages; ++i) {
         T *= m->upsample_rates[i];
         const int64_t C = m->upsample_initial_channel >> (i + 1);
@@ -211,8 +215,10 @@ extern "C" size_t bvg_workspace_bytes(const bvg_model_desc* m, int64_t B, int64_
 }
 
 // wav_dtype: BVG_F32 (the module's output) or BVG_I16 (the caller's PCM conversion fused into the tail kernel)
-static int forward_impl(const bvg_model_desc* m, const float* mel, int64_t mel_stride_b, int64_t mel_stride_c, void* wav,
-                        int wav_dtype, int64_t B, int64_t T_mel, void* workspace, size_t workspace_bytes, void* stream) {
+// mel_layout 0: ncl with element strides; 1: dense nlc.  cond: nullptr or num_stages + 1 device pointers (v1 generator).
+static int forward_impl(const bvg_model_desc* m, const float* mel, int mel_layout, int64_t mel_stride_b,
+                        int64_t mel_stride_c, const float* const* cond, void* wav, int wav_dtype, int64_t B, int64_t T_mel,
+                        void* workspace, size_t workspace_bytes, void* stream) {
     BVG_REQUIRE(m && mel && wav, BVG_ERR_INVALID, "bvg_forward: null pointer");
     BVG_REQUIRE(B >= 0 && T_mel >= 0, BVG_ERR_INVALID, "bvg_forward: negative shape");
     if (B == 0 || T_mel == 0) return BVG_OK;
@@ -241,10 +247,17 @@ static int forward_impl(const bvg_model_desc* m, const float* mel, int64_t mel_s
     auto conv_bytes = [&](double cin, double cout, double k, double rows, bool res) {
         return es * rows * (cin + cout) + es * cin * cout * k + 4.0 * cout + (res ? es * rows * cout : 0.0);
     };
-    // mel [B, num_mels, T] -> [B, T, num_mels] in the operand dtype
+    BVG_REQUIRE(mel_layout == 0 || mel_layout == 1, BVG_ERR_INVALID, "bvg_forward: unknown input layout %d", mel_layout);
+    const bool amp2 = m->resblock == 2;
+    // mel [B, num_mels, T] -> [B, T, num_mels] in the operand dtype (an nlc input only changes dtype)
     {
     ProfScope ps(BVG_K_LAYOUT, -1, m->num_mels, m->num_mels, 0, 0, B * T_mel, 0.0, 0.0, st);
-    rc = transpose_any(mel, BVG_F32, mel_nlc, op_dt, B, m->num_mels, T_mel, mel_stride_b, mel_stride_c, st);
+    if (mel_layout == 0)
+        rc = transpose_any(mel, BVG_F32, mel_nlc, op_dt, B, m->num_mels, T_mel, mel_stride_b, mel_stride_c, st);
+    else if (tc)
+        rc = add_channel_vector(mel, BVG_F32, nullptr, mel_nlc, op_dt, B, T_mel, m->num_mels, st);
+    else
+        mel_nlc = const_cast<float*>(mel);  // fp32 mode reads the caller's tensor in place
     }
     if (rc != BVG_OK) return rc;
     // conv_pre (bigvgan.py:362): output feeds the first transposed conv directly -> operand dtype
@@ -252,8 +265,19 @@ static int forward_impl(const bvg_model_desc* m, const float* mel, int64_t mel_s
         const bvg_conv_desc& c = m->conv_pre;
         ProfScope ps(BVG_K_CONV1D, -1, c.cin, c.cout, c.k, 1, B * T_mel, conv_flops(c.cin, c.cout, c.k, (double)B * T_mel),
                      conv_bytes(c.cin, c.cout, c.k, (double)B * T_mel, false), st);
-        rc = conv1d(prec, mel_nlc, c.w, c.bias, nullptr, nullptr, tc ? nullptr : reinterpret_cast<float*>(pre),
-                    tc ? pre : nullptr, B, T_mel, c.cin, c.cout, c.k, 1, 1.0f, st);
+        BVG_REQUIRE(c.cin == m->num_mels && c.cout == m->upsample_initial_channel, BVG_ERR_INVALID, "conv_pre: channel mismatch");
+        const bool cond_pre = cond != nullptr && cond[0] != nullptr;
+        // conditioned (v1): fp32 result into X, the add below rounds to the operand dtype once
+        float* pre_f32 = cond_pre ? X : (tc ? nullptr : reinterpret_cast<float*>(pre));
+        rc = conv1d(prec, mel_nlc, c.w, c.bias, nullptr, nullptr, pre_f32, pre_f32 ? nullptr : pre, B, T_mel, c.cin, c.cout,
+                    c.k, 1, 1.0f, st);
+        if (rc != BVG_OK) return rc;
+    }
+    if (cond != nullptr && cond[0] != nullptr) {
+        // x = x + cond_layer(speaker_embedding)   (indextts/BigVGAN/models.py:236)
+        const double n = (double)B * T_mel * m->upsample_initial_channel;
+        ProfScope ps(BVG_K_COND, -1, m->upsample_initial_channel, m->upsample_initial_channel, 0, 0, B * T_mel, n, (4.0 + es) * n, st);
+        rc = add_channel_vector(X, BVG_F32, cond[0], pre, op_dt, B, T_mel, m->upsample_initial_channel, st);
         if (rc != BVG_OK) return rc;
     }
     const void* stage_in = pre;
@@ -274,6 +298,13 @@ static int forward_impl(const bvg_model_desc* m, const float* mel, int64_t mel_s
         if (rc != BVG_OK) return rc;
         T *= u;
         C /= 2;
+        if (cond != nullptr && cond[i + 1] != nullptr) {
+            // x = x + conds[i](speaker_embedding)   (indextts/BigVGAN/models.py:244-245), in place on the residual stream
+            const double n = (double)B * T * C;
+            ProfScope ps(BVG_K_COND, i, C, C, 0, 0, B * T, n, 8.0 * n, st);
+            rc = add_channel_vector(X, BVG_F32, cond[i + 1], X, BVG_F32, B, T, C, st);
+            if (rc != BVG_OK) return rc;
+        }
         const bool last_stage = (i + 1 == m->num_stages);
         // The AMP blocks all begin with an Activation1d of X (bigvgan.py:133-135): one launch computes the 2x up-sampling
         // of X once and applies the blocks' snake parameters to it (activation1d_nlc_multi), before the streams fork.
@@ -306,9 +337,9 @@ static int forward_impl(const bvg_model_desc* m, const float* mel, int64_t mel_s
             const float* xr = X;  // residual stream of this block (bigvgan.py:132-141)
             for (int l = 0; l < m->num_dilations; ++l) {
                 const bvg_conv_desc& c1 = m->convs1[i][j][l];
-                const bvg_conv_desc& c2 = m->convs2[i][j][l];
-                const bvg_act_desc& a1 = m->acts[i][j][2 * l];
-                const bvg_act_desc& a2 = m->acts[i][j][2 * l + 1];
+                const bvg_conv_desc& c2_ = m->convs2[i][j][l];
+                const bvg_act_desc& a1 = m->acts[i][j][amp2 ? l : 2 * l];
+                const bvg_act_desc& a2 = m->acts[i][j][amp2 ? l : 2 * l + 1];
                 const double rows = (double)B * T;
                 const double act_flops = 62.0 * rows * C, act_bytes = 2.0 * es * rows * C + 8.0 * C;
                 if (!(heads && l == 0)) {
@@ -318,19 +349,22 @@ static int forward_impl(const bvg_model_desc* m, const float* mel, int64_t mel_s
                 if (rc != BVG_OK) return rc;
                 // xt between c1 and a2 is an intermediate (not the residual stream): operand dtype (bf16 in TC mode;
                 // costs ~1.2 dB of the 43.8 dB budget, tools/emulate_bf16_plan.py)
-                {
+                if (!amp2) {
                     ProfScope ps(BVG_K_CONV1D, i, C, C, c1.k, c1.dilation, B * T, conv_flops(C, C, c1.k, rows),
                                  conv_bytes(C, C, c1.k, rows, false), sj);
                     rc = conv1d_desc(prec, c1, A, nullptr, nullptr, tc ? nullptr : reinterpret_cast<float*>(Y1),
                                      tc ? Y1 : nullptr, B, T, C, 1.0f, sj);
                 }
                 if (rc != BVG_OK) return rc;
-                {
+                if (!amp2) {
                     ProfScope ps(BVG_K_ACT, i, C, C, 0, 0, B * T, act_flops, act_bytes, sj);
                     rc = activation1d_nlc(Y1, op_dt, A, op_dt, a2.alpha_log, a2.beta_log, B, T, C, precise, sj);
                 }
                 if (rc != BVG_OK) return rc;
-                ProfScope ps(BVG_K_CONV1D, i, C, C, c2.k, 1, B * T, conv_flops(C, C, c2.k, rows),
+                // AMPBlock2: the block's only conv of this dilation carries the residual add (the conv the code below
+                // calls c2 is convs1[l], dilated)
+                const bvg_conv_desc& c2 = amp2 ? c1 : c2_;
+                ProfScope ps(BVG_K_CONV1D, i, C, C, c2.k, c2.dilation, B * T, conv_flops(C, C, c2.k, rows),
                              conv_bytes(C, C, c2.k, rows, true), sj);
                 const bool last = (l + 1 == m->num_dilations);
                 if (!last) {
@@ -374,13 +408,22 @@ static int forward_impl(const bvg_model_desc* m, const float* mel, int64_t mel_s
 
 extern "C" int bvg_forward(const bvg_model_desc* m, const float* mel, int64_t mel_stride_b, int64_t mel_stride_c,
                            float* wav, int64_t B, int64_t T_mel, void* workspace, size_t workspace_bytes, void* stream) {
-    return forward_impl(m, mel, mel_stride_b, mel_stride_c, wav, BVG_F32, B, T_mel, workspace, workspace_bytes, stream);
+    return forward_impl(m, mel, 0, mel_stride_b, mel_stride_c, nullptr, wav, BVG_F32, B, T_mel, workspace, workspace_bytes,
+                        stream);
+}
+
+extern "C" int bvg_forward_cond(const bvg_model_desc* m, const float* x, int x_layout, int64_t x_stride_b,
+                                int64_t x_stride_c, const float* const* cond_host, float* wav, int64_t B, int64_t T,
+                                void* workspace, size_t workspace_bytes, void* stream) {
+    return forward_impl(m, x, x_layout, x_stride_b, x_stride_c, cond_host, wav, BVG_F32, B, T, workspace, workspace_bytes,
+                        stream);
 }
 
 extern "C" int bvg_forward_pcm16(const bvg_model_desc* m, const float* mel, int64_t mel_stride_b, int64_t mel_stride_c,
                                  int16_t* pcm, int64_t B, int64_t T_mel, void* workspace, size_t workspace_bytes,
                                  void* stream) {
-    return forward_impl(m, mel, mel_stride_b, mel_stride_c, pcm, BVG_I16, B, T_mel, workspace, workspace_bytes, stream);
+    return forward_impl(m, mel, 0, mel_stride_b, mel_stride_c, nullptr, pcm, BVG_I16, B, T_mel, workspace, workspace_bytes,
+                        stream);
 }
 
 extern "C" int bvg_forward_profile(const bvg_model_desc* m, const float* mel, int64_t mel_stride_b, int64_t mel_stride_c,

@@ -244,6 +244,43 @@ def conv_post(x_nlc: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor]
     return y
 
 
+# ---------------------------------------------------------------------------------------------------------------
+# v1 generator conditioning (reference indextts/BigVGAN/models.py:197-202, 236, 244-245)
+# ---------------------------------------------------------------------------------------------------------------
+def cond_linear(e: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor]) -> torch.Tensor:
+    """``Conv1d(D, C, 1)`` applied to the length-1 speaker embedding: ``e`` ``[B, D]`` fp32, ``w`` ``[C, D]`` or
+    ``[C, D, 1]`` -> ``[B, C]`` fp32."""
+    _require_cuda(e, "cond_linear")
+    e = e.detach().float().contiguous()
+    w = w.detach().float().contiguous()
+    B, D = e.shape
+    C = w.shape[0]
+    if w.numel() != C * D:
+        raise _lib.BvgError(f"cond_linear: weight {tuple(w.shape)} does not match an embedding of width {D}")
+    b = None if bias is None else bias.detach().float().contiguous()
+    y = torch.empty((B, C), dtype=torch.float32, device=e.device)
+    with torch.cuda.device(e.device):
+        check(_lib.load().bvg_cond_linear_fwd(e.data_ptr(), w.data_ptr(), _ptr(b), y.data_ptr(), B, D, C, _stream()),
+              "bvg_cond_linear_fwd")
+    return y
+
+
+def add_channel_vector_nlc(x: torch.Tensor, v: Optional[torch.Tensor], out_dtype: torch.dtype) -> torch.Tensor:
+    """``x[b, t, c] + v[b, c]`` on a channels-last tensor (``v`` None: dtype conversion only)."""
+    _require_cuda(x, "add_channel_vector_nlc")
+    x = x.contiguous()
+    B, T, C = x.shape
+    if v is not None:
+        v = v.detach().float().contiguous()
+        if tuple(v.shape) != (B, C):
+            raise _lib.BvgError(f"add_channel_vector_nlc: vector must be [{B}, {C}], got {tuple(v.shape)}")
+    y = torch.empty((B, T, C), dtype=out_dtype, device=x.device)
+    with torch.cuda.device(x.device):
+        check(_lib.load().bvg_add_channel_vector_nlc(x.data_ptr(), _dt(x, "add_channel_vector_nlc"), _ptr(v), y.data_ptr(),
+                                                     _DT[out_dtype], B, T, C, _stream()), "bvg_add_channel_vector_nlc")
+    return y
+
+
 def launch_count() -> int:
     return int(_lib.load().bvg_launch_count())
 

@@ -33,6 +33,8 @@ __all__ = [
     "get_padding",
     "effective_weights",
     "forward",
+    "forward_v1",
+    "V1_HPARAMS",
     "forward_time_sharded",
     "make_state_dict",
     "load_hparams",
@@ -55,6 +57,26 @@ DEFAULT_HPARAMS = {
     "num_mels": 80,
     "hop_size": 256,
     "sampling_rate": 22050,
+}
+
+# Generator section of the v1 model (indextts/BigVGAN/models.py:130-200 reads these keys).  The v1 checkpoint's config file
+# is a download and NOT part of the reference tree: the values below are the shape class upstream IndexTTS v1 publishes
+# (24 kHz, 1024x up-sampling of the 1024-wide GPT latent, 512-wide speaker embedding); tests use scaled-down versions.
+V1_HPARAMS = {
+    "resblock": "1",
+    "upsample_rates": [4, 4, 4, 4, 2, 2],
+    "upsample_kernel_sizes": [8, 8, 4, 4, 4, 4],
+    "upsample_initial_channel": 1536,
+    "resblock_kernel_sizes": [3, 7, 11],
+    "resblock_dilation_sizes": [[1, 3, 5], [1, 3, 5], [1, 3, 5]],
+    "activation": "snakebeta",
+    "snake_logscale": True,
+    "feat_upsample": False,
+    "cond_d_vector_in_each_upsampling_layer": True,
+    "speaker_embedding_dim": 512,
+    "gpt_dim": 1024,
+    "num_mels": 100,
+    "sampling_rate": 24000,
 }
 
 # one-sided receptive field of the whole generator in mel frames.
@@ -284,6 +306,73 @@ def _amp_block1(sd, prefix, x, k, dilations, logscale, dtype, filt):
     return x
 
 
+def _act(sd, prefix, x, h, dtype, filt):
+    """``Activation1d`` of a ``Snake`` (BV/activations.py:54-57: beta := alpha, no ``.act.beta`` key) or ``SnakeBeta``."""
+    alpha = np.asarray(sd[f"{prefix}.act.alpha"])
+    beta = np.asarray(sd[f"{prefix}.act.beta"]) if h["activation"] == "snakebeta" else alpha
+    return activation1d(x, alpha, beta, bool(h["snake_logscale"]), filt)
+
+
+def _amp_block2(sd, prefix, x, k, dilations, h, dtype, filt):
+    """``AMPBlock2.forward`` as upstream wrote it (indextts/BigVGAN/bigvgan.py:231-236, indextts/BigVGAN/models.py:117-123):
+    act -> conv(d) -> +x per dilation.  The copy at BV/bigvgan.py:232-236 lacks the ``return x``."""
+    for l, d in enumerate(dilations):
+        xt = _act(sd, f"{prefix}.activations.{l}", x, h, dtype, filt)
+        xt = conv1d(xt, effective_weights(sd, f"{prefix}.convs.{l}", dtype), _bias(sd, f"{prefix}.convs.{l}", dtype),
+                    dilation=d)
+        x = xt + x
+    return x
+
+
+def _amp_block(sd, prefix, x, k, dilations, h, dtype, filt):
+    if h["resblock"] == "2":
+        return _amp_block2(sd, prefix, x, k, dilations, h, dtype, filt)
+    if h["activation"] == "snakebeta":
+        return _amp_block1(sd, prefix, x, k, dilations, bool(h["snake_logscale"]), dtype, filt)
+    # AMPBlock1 with Snake activations
+    for l, d in enumerate(dilations):
+        xt = _act(sd, f"{prefix}.activations.{2 * l}", x, h, dtype, filt)
+        xt = conv1d(xt, effective_weights(sd, f"{prefix}.convs1.{l}", dtype), _bias(sd, f"{prefix}.convs1.{l}", dtype),
+                    dilation=d)
+        xt = _act(sd, f"{prefix}.activations.{2 * l + 1}", xt, h, dtype, filt)
+        xt = conv1d(xt, effective_weights(sd, f"{prefix}.convs2.{l}", dtype), _bias(sd, f"{prefix}.convs2.{l}", dtype))
+        x = xt + x
+    return x
+
+
+def forward_v1(sd: Mapping[str, np.ndarray], x: np.ndarray, speaker_embedding: np.ndarray, h: Optional[Mapping] = None,
+               dtype=np.float32) -> np.ndarray:
+    """indextts/BigVGAN/models.py:201-258 ``BigVGAN.forward`` of the v1 generator AFTER the speaker encoder (:202):
+    ``x`` ``[B, T, gpt_dim]`` latent, ``speaker_embedding`` ``[B, D]`` -> ``[B, 1, T*prod(rates)]``.
+    ``feat_upsample`` (:214-219, a 4x linear interpolation of the latent) must be false, as in the published config."""
+    h = dict(V1_HPARAMS if h is None else h)
+    assert not h.get("feat_upsample", False)
+    filt = kaiser_sinc_filter1d(dtype=np.float32).astype(dtype)
+    e = np.asarray(speaker_embedding).astype(dtype)
+
+    def cond(prefix):  # Conv1d(D, C, 1) on the [B, D, 1] embedding (:197-202): [B, C, 1]
+        w = np.asarray(sd[prefix + ".weight"]).astype(dtype)[:, :, 0]
+        return (e @ w.T + np.asarray(sd[prefix + ".bias"]).astype(dtype))[:, :, None]
+
+    x = np.asarray(x).astype(dtype).transpose(0, 2, 1)  # :221
+    x = conv1d(x, effective_weights(sd, "conv_pre", dtype), _bias(sd, "conv_pre", dtype))
+    x = x + cond("cond_layer")  # :236
+    nk = len(h["resblock_kernel_sizes"])
+    for i, (u, k) in enumerate(zip(h["upsample_rates"], h["upsample_kernel_sizes"])):
+        x = conv_transpose1d(x, effective_weights(sd, f"ups.{i}.0", dtype), _bias(sd, f"ups.{i}.0", dtype),
+                             stride=u, padding=(k - u) // 2)
+        if h.get("cond_d_vector_in_each_upsampling_layer", False):
+            x = x + cond(f"conds.{i}")  # :244-245
+        xs = None
+        for j, (rk, rd) in enumerate(zip(h["resblock_kernel_sizes"], h["resblock_dilation_sizes"])):
+            r = _amp_block(sd, f"resblocks.{i * nk + j}", x, rk, rd, h, dtype, filt)
+            xs = r if xs is None else xs + r
+        x = xs / dtype(nk)
+    x = _act(sd, "activation_post", x, h, dtype, filt)
+    x = conv1d(x, effective_weights(sd, "conv_post", dtype), _bias(sd, "conv_post", dtype))
+    return np.tanh(x)  # :256
+
+
 def forward(sd: Mapping[str, np.ndarray], mel: np.ndarray, h: Optional[Mapping] = None,
             dtype=np.float32, taps: Optional[Dict[str, np.ndarray]] = None) -> np.ndarray:
     """BV/bigvgan.py:360-386 ``BigVGAN.forward``: ``[B, num_mels, T] -> [B, 1, T*prod(rates)]``.
@@ -291,9 +380,7 @@ def forward(sd: Mapping[str, np.ndarray], mel: np.ndarray, h: Optional[Mapping] 
     ``taps`` (optional dict) receives named intermediates for per-layer parity tests.
     """
     h = dict(DEFAULT_HPARAMS if h is None else h)
-    assert h["resblock"] == "1", "oracle restates AMPBlock1 only (config.json:2)"
-    assert h["activation"] == "snakebeta"
-    logscale = bool(h["snake_logscale"])
+    assert h["resblock"] in ("1", "2") and h["activation"] in ("snake", "snakebeta")
     filt = kaiser_sinc_filter1d(dtype=np.float32).astype(dtype)
     x = np.asarray(mel).astype(dtype)
     x = conv1d(x, effective_weights(sd, "conv_pre", dtype), _bias(sd, "conv_pre", dtype))
@@ -307,13 +394,12 @@ def forward(sd: Mapping[str, np.ndarray], mel: np.ndarray, h: Optional[Mapping] 
             taps[f"ups.{i}"] = x
         xs = None
         for j, (rk, rd) in enumerate(zip(h["resblock_kernel_sizes"], h["resblock_dilation_sizes"])):
-            r = _amp_block1(sd, f"resblocks.{i * nk + j}", x, rk, rd, logscale, dtype, filt)
+            r = _amp_block(sd, f"resblocks.{i * nk + j}", x, rk, rd, h, dtype, filt)
             xs = r if xs is None else xs + r
         x = xs / dtype(nk)
         if taps is not None:
             taps[f"stage.{i}"] = x
-    x = activation1d(x, np.asarray(sd["activation_post.act.alpha"]), np.asarray(sd["activation_post.act.beta"]),
-                     logscale, filt)
+    x = _act(sd, "activation_post", x, h, dtype, filt)
     x = conv1d(x, effective_weights(sd, "conv_post", dtype), _bias(sd, "conv_post", dtype))
     if taps is not None:
         taps["conv_post"] = x
@@ -374,12 +460,14 @@ def make_state_dict(h: Optional[Mapping] = None, seed: int = 0, weight_norm: boo
 
     def act(prefix, c):
         sd[prefix + ".act.alpha"] = (alpha_beta_std * rng.standard_normal(c)).astype(np.float32)
-        sd[prefix + ".act.beta"] = (alpha_beta_std * rng.standard_normal(c)).astype(np.float32)
+        if h["activation"] == "snakebeta":
+            sd[prefix + ".act.beta"] = (alpha_beta_std * rng.standard_normal(c)).astype(np.float32)
         sd[prefix + ".upsample.filter"] = filt.copy()
         sd[prefix + ".downsample.lowpass.filter"] = filt.copy()
 
     c0 = h["upsample_initial_channel"]
-    conv("conv_pre", c0, h["num_mels"], 7)
+    v1 = "gpt_dim" in h  # v1 generator (indextts/BigVGAN/models.py): latent input, speaker conditioning, biased conv_post
+    conv("conv_pre", c0, h["gpt_dim"] if v1 else h["num_mels"], 7)
     nk = len(h["resblock_kernel_sizes"])
     ch = c0
     for i, (u, k) in enumerate(zip(h["upsample_rates"], h["upsample_kernel_sizes"])):
@@ -387,6 +475,11 @@ def make_state_dict(h: Optional[Mapping] = None, seed: int = 0, weight_norm: boo
         ch = c0 // 2 ** (i + 1)
         for j, (rk, rd) in enumerate(zip(h["resblock_kernel_sizes"], h["resblock_dilation_sizes"])):
             p = f"resblocks.{i * nk + j}"
+            if h["resblock"] == "2":
+                for l in range(len(rd)):
+                    conv(f"{p}.convs.{l}", ch, ch, rk)
+                    act(f"{p}.activations.{l}", ch)
+                continue
             for l in range(len(rd)):
                 conv(f"{p}.convs1.{l}", ch, ch, rk)
                 conv(f"{p}.convs2.{l}", ch, ch, rk)
@@ -394,6 +487,14 @@ def make_state_dict(h: Optional[Mapping] = None, seed: int = 0, weight_norm: boo
                 act(f"{p}.activations.{m}", ch)
     act("activation_post", ch)
     conv("conv_post", 1, ch, 7, bias=bool(h.get("use_bias_at_final", True)))
+    if v1:  # plain (not weight-normed) 1x1 convs, models.py:197-202
+        wn, weight_norm = weight_norm, False
+        D = h["speaker_embedding_dim"]
+        conv("cond_layer", c0, D, 1)
+        if h.get("cond_d_vector_in_each_upsampling_layer", False):
+            for i in range(len(h["upsample_rates"])):
+                conv(f"conds.{i}", c0 // 2 ** (i + 1), D, 1)
+        weight_norm = wn
     return sd
 
 

@@ -103,3 +103,21 @@ def test_time_sharding_with_halo_equals_unsharded():
     # too small a halo must be visible (guards against a vacuous test)
     bad = O.forward_time_sharded(sd, mel, 2, MINI_H, np.float32, halo=2)
     assert np.abs(bad - full).max() > 1e-6
+
+
+VARIANTS = ["v1", "v1_amp2", "v1_amp2_snake", "v1_amp1_snake_nocond"]
+
+
+@pytest.mark.parametrize("tag", VARIANTS)
+def test_v1_generator_variants_match_reference(golden_dir, tag):
+    """The conditioned v1 generator (indextts/BigVGAN/models.py:201-258 after the speaker encoder) and the AMPBlock2 /
+    Snake configurations, against outputs of the reference itself (tests/golden/make_golden_variants.py)."""
+    import json
+    g = _load(golden_dir, "variants.npz")
+    h = json.loads(str(g[f"{tag}_h"]))
+    sd = O.make_state_dict(h, seed=int(g[f"{tag}_seed"]))
+    wav = O.forward_v1(sd, g[f"{tag}_x"], g[f"{tag}_emb"], h, np.float32)
+    ref = g[f"{tag}_wav"]
+    assert wav.shape == ref.shape
+    assert np.abs(wav - ref).max() < 2e-5, np.abs(wav - ref).max()
+    assert O.snr_db(ref, wav) > 100
