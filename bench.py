@@ -161,6 +161,7 @@ def main():
     ap.add_argument("--frames", type=int, default=CFG2_T)
     ap.add_argument("--precision", default="bf16")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-v1", action="store_true", help="skip the v1-generator leg")
     ap.add_argument("--layer-table", default=None, help="write the per-launch table (JSON) to this path")
     args = ap.parse_args()
     # stdout carries exactly ONE JSON line: everything else that writes to fd 1 (NCCL's version banner, the reference's
@@ -308,6 +309,42 @@ def main():
         os.makedirs(os.path.dirname(os.path.abspath(args.layer_table)), exist_ok=True)
         json.dump({"workload": WORKLOAD, "batch": Bsz, "frames": T, "peaks": peaks, "records": recs}, open(args.layer_table, "w"), indent=1)
 
+    # ---- v1 generator leg (reference indextts/BigVGAN/models.py): the conditioned 24 kHz / 1024x
+    # generator through its public forward(x, mel_ref) -- ECAPA-TDNN speaker encoder (torch) + bvg_forward_cond -- on
+    # 16 x 10 s of synthetic GPT latents, and the decoder alone with the embedding given.
+    v1_line = None
+    if not args.no_v1 and world == 1:  # timed() barriers across ranks; the other ranks have left by now
+        from index_tts_b200 import v1 as V1
+        hv = B.AttrDict(dict(V1.DEFAULT_HPARAMS))
+        torch.manual_seed(4321)
+        mv = V1.BigVGAN(hv, use_cuda_kernel=True)
+        with torch.no_grad():
+            for n_, p_ in mv.named_parameters():
+                if n_.endswith(".alpha") or n_.endswith(".beta"):
+                    p_.normal_(0.0, 0.5)
+        mv.remove_weight_norm()
+        mv = mv.to(dev).eval().set_precision(args.precision)
+        Tv = 235  # 235 latent frames x 1024 / 24 kHz = 10.03 s
+        gv = torch.Generator().manual_seed(3)
+        xv = torch.randn(Bsz, Tv, hv.gpt_dim, generator=gv).to(dev)
+        melv = torch.randn(Bsz, 300, hv.num_mels, generator=gv).to(dev)
+        with torch.no_grad():
+            embv = mv.speaker_encoder(melv)
+        fv = lambda: mv(xv, melv)
+        fd = lambda: mv.forward_with_embedding(xv, embv)
+        with torch.no_grad():
+            for _ in range(3):
+                fv()
+            ms_v1 = timed(fv, 3)
+            fd()
+            ms_v1d = timed(fd, 3)
+        audio_v1 = Bsz * Tv * 1024 / 24000.0
+        v1_line = {"workload": "v1 generator (models.py shape class: 1536 ch, rates 4,4,4,4,2,2, gpt_dim 1024, D 512), "
+                               f"batch {Bsz} x {Tv} latent frames (10 s each), random-init, {args.precision}",
+                   "value": audio_v1 / (ms_v1 * 1e-3), "unit": "audio-s/s", "ms_per_step": ms_v1,
+                   "decoder_only_ms": ms_v1d, "decoder_only_value": audio_v1 / (ms_v1d * 1e-3)}
+        del mv, xv, melv
+
     cpu = None
     if not args.no_cpu_baseline:
         v, dt, threads, sample = cpu_port_audio_s_per_s(steps=3, warmup=1)
@@ -330,6 +367,7 @@ def main():
                                "definition": "sum over layers of max(FLOPs/bf16 sustained peak, algorithmic bytes/HBM peak) / sum of CUDA-event kernel times"},
         "kernels": kernels,
         "long_form": long_form,
+        "v1_generator": v1_line,
         "cpu_baseline": cpu,
     }
     emit(line)

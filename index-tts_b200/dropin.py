@@ -36,6 +36,22 @@ _ALIASES = {
     ".alias_free_activation.cuda.activation1d": "index_tts_b200.alias_free_activation.cuda.activation1d",
     ".alias_free_activation.cuda.load": "index_tts_b200.alias_free_activation.cuda.load",
 }
+# the v1 pipeline's vocoder (indextts/infer.py:29 `from indextts.BigVGAN.models import BigVGAN as Generator`, :116-121 the
+# kernel preload `from indextts.BigVGAN.alias_free_activation.cuda import load; load.load()`)
+V1_REFERENCE_PACKAGE = "indextts.BigVGAN"
+_V1_ALIASES = {
+    "": "index_tts_b200",
+    ".models": "index_tts_b200.v1",
+    ".ECAPA_TDNN": "index_tts_b200.ecapa",
+    ".activations": "index_tts_b200.activations",
+    ".utils": "index_tts_b200.utils",
+    ".alias_free_torch": "index_tts_b200.alias_free_activation.torch",
+    ".alias_free_activation": "index_tts_b200.alias_free_activation",
+    ".alias_free_activation.torch": "index_tts_b200.alias_free_activation.torch",
+    ".alias_free_activation.cuda": "index_tts_b200.alias_free_activation.cuda",
+    ".alias_free_activation.cuda.activation1d": "index_tts_b200.alias_free_activation.cuda.activation1d",
+    ".alias_free_activation.cuda.load": "index_tts_b200.alias_free_activation.cuda.load",
+}
 _installed = {}
 
 
@@ -59,12 +75,13 @@ def _ensure_parent_packages():
 
 
 def install(preload_kernels: bool = True):
-    """Alias this package as ``indextts.s2mel.modules.bigvgan`` (idempotent).  With ``preload_kernels`` the shared
+    """Alias this package as ``indextts.s2mel.modules.bigvgan`` and, for the v1 pipeline, ``indextts.BigVGAN`` (idempotent).  With ``preload_kernels`` the shared
     library is loaded right away, so a missing ``libbvg.so`` fails here, loudly, instead of at the first forward."""
     _ensure_parent_packages()
-    for rel, ours in _ALIASES.items():
+    table = [(REFERENCE_PACKAGE + rel, ours) for rel, ours in _ALIASES.items()]
+    table += [(V1_REFERENCE_PACKAGE + rel, ours) for rel, ours in _V1_ALIASES.items()]
+    for name, ours in table:
         mod = importlib.import_module(ours)
-        name = REFERENCE_PACKAGE + rel
         sys.modules[name] = mod
         _installed[name] = mod
         parent, _, leaf = name.rpartition(".")

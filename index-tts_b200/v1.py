@@ -26,6 +26,26 @@ from .utils import init_weights
 
 LRELU_SLOPE = 0.1
 
+# Shape class of the published v1 vocoder (24 kHz, 1024x up-sampling of the 1024-wide GPT latent, 512-wide speaker
+# embedding, 100-band reference mel).  The v1 checkpoint's config file is a download, NOT part of the reference tree, so
+# these values are not pinned by it; `BigVGAN(h)` takes whatever `cfg.bigvgan` holds (infer.py:125).  Used by bench.py.
+DEFAULT_HPARAMS = {
+    "resblock": "1",
+    "upsample_rates": [4, 4, 4, 4, 2, 2],
+    "upsample_kernel_sizes": [8, 8, 4, 4, 4, 4],
+    "upsample_initial_channel": 1536,
+    "resblock_kernel_sizes": [3, 7, 11],
+    "resblock_dilation_sizes": [[1, 3, 5], [1, 3, 5], [1, 3, 5]],
+    "activation": "snakebeta",
+    "snake_logscale": True,
+    "feat_upsample": False,
+    "cond_d_vector_in_each_upsampling_layer": True,
+    "speaker_embedding_dim": 512,
+    "gpt_dim": 1024,
+    "num_mels": 100,
+    "sampling_rate": 24000,
+}
+
 __all__ = ["AMPBlock1", "AMPBlock2", "BigVGAN", "LRELU_SLOPE"]
 
 

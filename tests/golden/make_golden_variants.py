@@ -52,7 +52,8 @@ def main():
     # class, scaled down), AMPBlock2/SnakeBeta, AMPBlock2/Snake, AMPBlock1/Snake without the per-stage conditioning.
     variants = {
         "v1": dict(V1_MINI_H),
-        "v1_amp2": dict(V1_MINI_H, resblock="2", upsample_initial_channel=256, resblock_dilation_sizes=[[1, 3]] * 3),
+        "v1_amp2": dict(V1_MINI_H, resblock="2", upsample_initial_channel=256, resblock_dilation_sizes=[[1, 3]] * 3,
+                        upsample_rates=[4, 4, 2, 2], upsample_kernel_sizes=[8, 8, 4, 4]),
         "v1_amp2_snake": dict(V1_MINI_H, resblock="2", activation="snake", upsample_initial_channel=256,
                               resblock_dilation_sizes=[[1, 3]] * 3,  # models.py:79-93 hard-codes two convs
                               upsample_rates=[4, 2, 2], upsample_kernel_sizes=[8, 4, 4]),

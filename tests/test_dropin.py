@@ -36,8 +36,14 @@ _RESOLVE = textwrap.dedent(
     m.remove_weight_norm()
     m.eval()
     assert m.h["use_cuda_kernel"] is True
+    # v1 pipeline: infer.py:29 and the preload at infer.py:116-121
+    from indextts.BigVGAN.models import BigVGAN as Generator
+    import index_tts_b200.v1 as ours_v1
+    assert Generator is ours_v1.BigVGAN
+    from indextts.BigVGAN.alias_free_activation.cuda import load
+    assert "libbvg" in repr(load.load())
     dropin.uninstall()
-    assert "indextts.s2mel.modules.bigvgan.bigvgan" not in sys.modules
+    assert "indextts.s2mel.modules.bigvgan.bigvgan" not in sys.modules and "indextts.BigVGAN.models" not in sys.modules
     print("ok")
     """)
 

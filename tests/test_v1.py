@@ -98,7 +98,7 @@ def test_gpu_v1_generator_variants_bf16(golden_dir, tag):
 @pytest.mark.gpu
 def test_gpu_v1_forward_with_speaker_encoder_and_batch_independence():
     """``forward(x, mel_ref)`` = speaker encoder + decoder; every utterance gets ITS OWN conditioning vector."""
-    h = dict(V1_MINI_H, upsample_initial_channel=256)
+    h = dict(V1_MINI_H)
     m = _build_v1(h, O.make_state_dict(h, seed=31), "fp32")
     gen = torch.Generator().manual_seed(5)
     x = torch.randn(3, 6, h["gpt_dim"], generator=gen).cuda()
@@ -141,7 +141,7 @@ def test_gpu_cond_kernels_match_oracle():
 @pytest.mark.parametrize("activation", ["snakebeta", "snake"])
 def test_gpu_v2_generator_with_ampblock2_plan(activation):
     """``resblock "2"`` through the fused v2 launch plan (bvg_model_desc::resblock = 2) against the oracle."""
-    h = dict(O.DEFAULT_HPARAMS, resblock="2", activation=activation, upsample_initial_channel=256)
+    h = dict(O.DEFAULT_HPARAMS, resblock="2", activation=activation, upsample_initial_channel=512)
     sd = O.make_state_dict(h, seed=41)
     mel = np.random.default_rng(8).standard_normal((2, 80, 21)).astype(np.float32)
     ref = O.forward(sd, mel, h, np.float64)
