@@ -16,6 +16,7 @@ struct ConvSimtParams {
     const float* x;  // [B,T,Cin]
     const float* w;  // [taps][N][Cin]
     const float* bias;
+    const float* cond;  // per-utterance bias [B, cout_phase] or null (v1 generator conditioning, models.py:236, 244-245)
     const float* residual;
     const float* accum;
     float* y_f32;
@@ -91,12 +92,17 @@ conv_simt_kernel(const __grid_constant__ ConvSimtParams p) {
     if (ch >= p.cout_phase) return;
     float4 bias4 = make_float4(0.f, 0.f, 0.f, 0.f);
     if (p.bias) bias4 = __ldg(reinterpret_cast<const float4*>(p.bias + ch));
+    float4 cond4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (p.cond) cond4 = __ldg(reinterpret_cast<const float4*>(p.cond + b * p.cout_phase + ch));
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
         const int64_t t = t0 + ty * 8 + i;
         if (t >= p.T) break;
         const int64_t off = (b * p.T + t) * p.N + phase * p.cout_phase + ch;
         float o[4] = {acc[i][0] + bias4.x, acc[i][1] + bias4.y, acc[i][2] + bias4.z, acc[i][3] + bias4.w};
+        if (p.cond) {  // after the bias, like the reference's separate add of the 1x1 conv output
+            o[0] += cond4.x; o[1] += cond4.y; o[2] += cond4.z; o[3] += cond4.w;
+        }
         if (p.residual) {
             const float4 r = *reinterpret_cast<const float4*>(p.residual + off);
             o[0] += r.x; o[1] += r.y; o[2] += r.z; o[3] += r.w;
@@ -119,7 +125,8 @@ conv_simt_kernel(const __grid_constant__ ConvSimtParams p) {
 
 int conv_simt_launch(const void* x, const void* w_packed, const float* bias, const float* residual, const float* accum,
                      float* y_f32, void* y_bf16, int64_t B, int64_t T, int64_t Cin, int64_t N, int64_t cout_phase,
-                     int taps, int dil, const int* tap_base, int num_phases, float out_scale, cudaStream_t st) {
+                     int taps, int dil, const int* tap_base, int num_phases, float out_scale, cudaStream_t st,
+                     const float* cond) {
     BVG_REQUIRE(x && w_packed && (y_f32 || y_bf16), BVG_ERR_INVALID, "conv_simt: null pointer");
     BVG_REQUIRE(Cin % 4 == 0 && cout_phase % 4 == 0 && N == cout_phase * num_phases, BVG_ERR_UNSUPPORTED,
                 "conv_simt: Cin=%lld and Cout=%lld must be multiples of 4", (long long)Cin, (long long)cout_phase);
@@ -128,7 +135,7 @@ int conv_simt_launch(const void* x, const void* w_packed, const float* bias, con
     if (B == 0 || T == 0) return BVG_OK;
     ConvSimtParams p{};
     p.x = static_cast<const float*>(x); p.w = static_cast<const float*>(w_packed);
-    p.bias = bias; p.residual = residual; p.accum = accum; p.y_f32 = y_f32;
+    p.bias = bias; p.cond = cond; p.residual = residual; p.accum = accum; p.y_f32 = y_f32;
     p.y_bf16 = static_cast<__nv_bfloat16*>(y_bf16);
     p.T = T; p.Cin = (int)Cin; p.N = (int)N; p.cout_phase = (int)cout_phase; p.taps = taps; p.dil = dil;
     p.num_phases = num_phases; p.tiles_per_phase = (int)ceil_div(cout_phase, SIMT_BN); p.out_scale = out_scale;

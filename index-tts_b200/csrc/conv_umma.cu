@@ -46,6 +46,7 @@ constexpr int EPI_ST16_TILE_BYTES = 32 * 64;   // per-warp bf16 output chunk: 32
 
 struct ConvUmmaParams {
     const float* bias;      // [cout_phase] or null
+    const float* cond;      // per-utterance bias [B, cout_phase] or null (v1 generator conditioning)
     const float* residual;  // [B,T,N] fp32 or null
     const float* accum;     // [B,T,N] fp32 or null
     float* y_f32;           // [B,T,N] or null
@@ -488,6 +489,17 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                         }
                     }
                 }
+                if (p.cond) {  // warp-uniform addresses: one broadcast transaction per float4
+                    const int chb = c0 + c;
+                    const float* cv = p.cond + static_cast<size_t>(b) * p.cout_phase + chb;
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        if (chb + 4 * j < p.cout_phase) {
+                            const float4 bv = __ldg(reinterpret_cast<const float4*>(cv + 4 * j));
+                            o[4 * j] += bv.x; o[4 * j + 1] += bv.y; o[4 * j + 2] += bv.z; o[4 * j + 3] += bv.w;
+                        }
+                    }
+                }
                 if (n_ld > 0) {
                     mbar_wait_warp(&ld_full[ls], pls);
                     const uint8_t* ld = sLdG + ls * n_ld * EPI_LD_TILE_BYTES + row * 128;
@@ -627,7 +639,8 @@ static int64_t conv_smem_budget() {
 // Generic launcher: plain conv (num_phases = 1) or polyphase transposed conv.
 int conv_umma_launch(const void* x, const void* w_packed, const float* bias, const float* residual, const float* accum,
                      float* y_f32, void* y_bf16, int64_t B, int64_t T, int64_t Cin, int64_t N, int64_t cout_phase,
-                     int taps, int dil, const int* tap_base, int num_phases, float out_scale, cudaStream_t st) {
+                     int taps, int dil, const int* tap_base, int num_phases, float out_scale, cudaStream_t st,
+                     const float* cond) {
     BVG_REQUIRE(x && w_packed && (y_f32 || y_bf16), BVG_ERR_INVALID, "conv_umma: null pointer");
     BVG_REQUIRE(Cin % 8 == 0 && cout_phase % 8 == 0 && N == cout_phase * num_phases, BVG_ERR_UNSUPPORTED,
                 "conv_umma: Cin=%lld and Cout=%lld must be multiples of 8", (long long)Cin, (long long)cout_phase);
@@ -640,7 +653,7 @@ int conv_umma_launch(const void* x, const void* w_packed, const float* bias, con
     if (B == 0 || T == 0) return BVG_OK;
 
     ConvUmmaParams p{};
-    p.bias = bias; p.residual = residual; p.accum = accum; p.y_f32 = y_f32;
+    p.bias = bias; p.cond = cond; p.residual = residual; p.accum = accum; p.y_f32 = y_f32;
     p.y_bf16 = static_cast<__nv_bfloat16*>(y_bf16);
     p.T = T; p.B = (int)B; p.Cin = (int)Cin; p.N = (int)N; p.cout_phase = (int)cout_phase;
     p.taps = taps; p.dil = dil; p.num_phases = num_phases; p.out_scale = out_scale;

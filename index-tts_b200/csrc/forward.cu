@@ -7,10 +7,12 @@
 namespace bvg {
 int conv_umma_launch(const void* x, const void* w_packed, const float* bias, const float* residual, const float* accum,
                      float* y_f32, void* y_bf16, int64_t B, int64_t T, int64_t Cin, int64_t N, int64_t cout_phase,
-                     int taps, int dil, const int* tap_base, int num_phases, float out_scale, cudaStream_t st);
+                     int taps, int dil, const int* tap_base, int num_phases, float out_scale, cudaStream_t st,
+                     const float* cond);
 int conv_simt_launch(const void* x, const void* w_packed, const float* bias, const float* residual, const float* accum,
                      float* y_f32, void* y_bf16, int64_t B, int64_t T, int64_t Cin, int64_t N, int64_t cout_phase,
-                     int taps, int dil, const int* tap_base, int num_phases, float out_scale, cudaStream_t st);
+                     int taps, int dil, const int* tap_base, int num_phases, float out_scale, cudaStream_t st,
+                     const float* cond);
 int activation1d_nlc(const void* x, int x_dtype, void* y, int y_dtype, const float* alpha, const float* beta,
                      int64_t B, int64_t T, int64_t C, int precise, cudaStream_t st);
 int activation1d_nlc_multi(const void* x, int x_dtype, void* const* ys, int y_dtype, const float* const* alphas,
@@ -24,23 +26,23 @@ int add_channel_vector(const void* x, int x_dtype, const float* v, void* y, int 
 static int conv_dispatch(int precision, const void* x, const void* w, const float* bias, const float* residual,
                          const float* accum, float* y_f32, void* y_bf16, int64_t B, int64_t T, int64_t Cin, int64_t N,
                          int64_t cout_phase, int taps, int dil, const int* tap_base, int num_phases, float out_scale,
-                         cudaStream_t st) {
+                         cudaStream_t st, const float* cond = nullptr) {
     if (precision == BVG_BF16_TC)
         return conv_umma_launch(x, w, bias, residual, accum, y_f32, y_bf16, B, T, Cin, N, cout_phase, taps, dil, tap_base,
-                                num_phases, out_scale, st);
+                                num_phases, out_scale, st, cond);
     if (precision == BVG_EXACT_F32)
         return conv_simt_launch(x, w, bias, residual, accum, y_f32, y_bf16, B, T, Cin, N, cout_phase, taps, dil, tap_base,
-                                num_phases, out_scale, st);
+                                num_phases, out_scale, st, cond);
     return set_error(BVG_ERR_UNSUPPORTED, "unknown precision mode %d", precision);
 }
 
 static int conv1d(int precision, const void* x, const void* w, const float* bias, const float* residual,
                   const float* accum, float* y_f32, void* y_bf16, int64_t B, int64_t T, int64_t Cin, int64_t Cout, int k,
-                  int dil, float out_scale, cudaStream_t st) {
+                  int dil, float out_scale, cudaStream_t st, const float* cond = nullptr) {
     BVG_REQUIRE(k % 2 == 1, BVG_ERR_UNSUPPORTED, "conv1d: kernel size %d must be odd ('same' padding)", k);
     const int base = -((k - 1) / 2) * dil;
     return conv_dispatch(precision, x, w, bias, residual, accum, y_f32, y_bf16, B, T, Cin, Cout, Cout, k, dil, &base, 1,
-                         out_scale, st);
+                         out_scale, st, cond);
 }
 
 // AMP-block conv through its descriptor: plain, or time-folded (bvg.h, bvg_conv_desc::fold) in tensor-core mode.
@@ -56,14 +58,15 @@ static int conv1d_desc(int precision, const bvg_conv_desc& c, const void* x, con
 }
 
 static int convtranspose1d(int precision, const void* x, const void* w, const float* bias, float* y_f32, void* y_bf16,
-                           int64_t B, int64_t Tin, int64_t Cin, int64_t Cout, int K, int u, cudaStream_t st) {
+                           int64_t B, int64_t Tin, int64_t Cin, int64_t Cout, int K, int u, cudaStream_t st,
+                           const float* cond = nullptr) {
     BVG_REQUIRE(u >= 1 && u <= BVG_MAX_PHASES && K % u == 0 && (K - u) % 2 == 0, BVG_ERR_UNSUPPORTED,
                 "convtranspose1d: need K %% u == 0, (K-u) even, u <= %d (got K=%d u=%d)", BVG_MAX_PHASES, K, u);
     const int taps = K / u, p = (K - u) / 2;
     int base[BVG_MAX_PHASES];
     for (int r = 0; r < u; ++r) base[r] = (r + p) / u - (taps - 1);
     return conv_dispatch(precision, x, w, bias, nullptr, nullptr, y_f32, y_bf16, B, Tin, Cin, (int64_t)u * Cout, Cout, taps,
-                         1, base, u, 1.0f, st);
+                         1, base, u, 1.0f, st, cond);
 }
 
 // ------------------------------------------------------------------------------------------------------------
@@ -181,6 +184,15 @@ static int act_multi_requested() {
     return v;
 }
 
+// BVG_COND_FUSED=0: the v1 conditioning vectors are added by separate kernels instead of in the conv epilogues (A/B)
+static int cond_fused_requested() {
+    static const int v = []() {
+        const char* e = getenv("BVG_COND_FUSED");
+        return (e != nullptr && e[0] == '0' && e[1] == 0) ? 0 : 1;
+    }();
+    return v;
+}
+
 static int concurrency_requested() {
     static const int v = []() {
         const char* e = getenv("BVG_STREAMS");
@@ -249,6 +261,7 @@ static int forward_impl(const bvg_model_desc* m, const float* mel, int mel_layou
     };
     BVG_REQUIRE(mel_layout == 0 || mel_layout == 1, BVG_ERR_INVALID, "bvg_forward: unknown input layout %d", mel_layout);
     const bool amp2 = m->resblock == 2;
+    const bool fused_cond = cond_fused_requested() != 0;
     // mel [B, num_mels, T] -> [B, T, num_mels] in the operand dtype (an nlc input only changes dtype)
     {
     ProfScope ps(BVG_K_LAYOUT, -1, m->num_mels, m->num_mels, 0, 0, B * T_mel, 0.0, 0.0, st);
@@ -267,13 +280,14 @@ static int forward_impl(const bvg_model_desc* m, const float* mel, int mel_layou
                      conv_bytes(c.cin, c.cout, c.k, (double)B * T_mel, false), st);
         BVG_REQUIRE(c.cin == m->num_mels && c.cout == m->upsample_initial_channel, BVG_ERR_INVALID, "conv_pre: channel mismatch");
         const bool cond_pre = cond != nullptr && cond[0] != nullptr;
-        // conditioned (v1): fp32 result into X, the add below rounds to the operand dtype once
-        float* pre_f32 = cond_pre ? X : (tc ? nullptr : reinterpret_cast<float*>(pre));
+        // conditioned (v1, indextts/BigVGAN/models.py:236): the per-utterance vector rides in the conv epilogue as a second
+        // bias (one rounding to the operand dtype).  BVG_COND_FUSED=0: fp32 result into X and a separate add kernel.
+        float* pre_f32 = (cond_pre && !fused_cond) ? X : (tc ? nullptr : reinterpret_cast<float*>(pre));
         rc = conv1d(prec, mel_nlc, c.w, c.bias, nullptr, nullptr, pre_f32, pre_f32 ? nullptr : pre, B, T_mel, c.cin, c.cout,
-                    c.k, 1, 1.0f, st);
+                    c.k, 1, 1.0f, st, (cond_pre && fused_cond) ? cond[0] : nullptr);
         if (rc != BVG_OK) return rc;
     }
-    if (cond != nullptr && cond[0] != nullptr) {
+    if (cond != nullptr && cond[0] != nullptr && !fused_cond) {
         // x = x + cond_layer(speaker_embedding)   (indextts/BigVGAN/models.py:236)
         const double n = (double)B * T_mel * m->upsample_initial_channel;
         ProfScope ps(BVG_K_COND, -1, m->upsample_initial_channel, m->upsample_initial_channel, 0, 0, B * T_mel, n, (4.0 + es) * n, st);
@@ -293,12 +307,14 @@ static int forward_impl(const bvg_model_desc* m, const float* mel, int mel_layou
             const double rin = (double)B * T;
             ProfScope ps(BVG_K_CONVT, i, C, C / 2, up.k, 1, B * T * u, 2.0 * C * (C / 2) * up.k * rin,
                          es * rin * (C + (C / 2) * (double)u) + es * (double)C * (C / 2) * up.k, st);
-            rc = convtranspose1d(prec, stage_in, up.w, up.bias, X, nullptr, B, T, C, C / 2, up.k, u, st);
+            // v1 (models.py:244-245): x = x + conds[i](speaker_embedding), fused into the epilogue of every phase
+            rc = convtranspose1d(prec, stage_in, up.w, up.bias, X, nullptr, B, T, C, C / 2, up.k, u, st,
+                                 (cond != nullptr && fused_cond) ? cond[i + 1] : nullptr);
         }
         if (rc != BVG_OK) return rc;
         T *= u;
         C /= 2;
-        if (cond != nullptr && cond[i + 1] != nullptr) {
+        if (cond != nullptr && cond[i + 1] != nullptr && !fused_cond) {
             // x = x + conds[i](speaker_embedding)   (indextts/BigVGAN/models.py:244-245), in place on the residual stream
             const double n = (double)B * T * C;
             ProfScope ps(BVG_K_COND, i, C, C, 0, 0, B * T, n, 8.0 * n, st);
