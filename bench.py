@@ -345,6 +345,24 @@ def main():
                    "decoder_only_ms": ms_v1d, "decoder_only_value": audio_v1 / (ms_v1d * 1e-3)}
         del mv, xv, melv
 
+    # ---- single-utterance latency (BASELINE.json configs[0] shape: one 5 s mel, 80x431; the reference pipeline calls the
+    # vocoder with B = 1, infer_v2.py:860): eager launch plan vs CUDA-graph replay (BigVGAN.set_cuda_graphs)
+    latency = None
+    if world == 1:
+        mel1 = torch.randn(1, NUM_MELS, 431, generator=torch.Generator().manual_seed(0)).to(dev)
+        f1 = lambda: model(mel1)
+        with torch.no_grad():
+            for _ in range(3):
+                f1()
+            ms_eager = timed(f1, 10)
+            model.set_cuda_graphs(4096)
+            for _ in range(3):
+                f1()
+            ms_graph = timed(f1, 10)
+            model.set_cuda_graphs(0)
+        latency = {"workload": "cfg1 shape: 1 x 5 s mel (80x431), " + args.precision, "eager_ms": ms_eager,
+                   "cuda_graph_ms": ms_graph, "audio_s_per_s_graph": (431 * HOP / SR) / (ms_graph * 1e-3)}
+
     cpu = None
     if not args.no_cpu_baseline:
         v, dt, threads, sample = cpu_port_audio_s_per_s(steps=3, warmup=1)
@@ -368,6 +386,7 @@ def main():
         "kernels": kernels,
         "long_form": long_form,
         "v1_generator": v1_line,
+        "latency": latency,
         "cpu_baseline": cpu,
     }
     emit(line)

@@ -13,9 +13,11 @@ kernels are the only implementation, and a CPU tensor or a non-sm_100 device rai
 """
 from __future__ import annotations
 
+import collections
 import ctypes
 import json
 import os
+import threading
 import weakref
 from pathlib import Path
 from typing import Dict, List, Optional, Union
@@ -366,6 +368,7 @@ class _PackedGenerator:
         d.conv_post.cin, d.conv_post.cout = int(cp.in_channels), int(cp.out_channels)
         d.conv_post.k, d.conv_post.dilation = int(cp.kernel_size[0]), 1
         self.desc = d
+        self.graph_max_frames = int(getattr(model, "_bvg_graph_max_frames", 0) or 0)
         self.plan_id = _next_plan_id[0]
         _next_plan_id[0] += 1
         _PLANS[self.plan_id] = self
@@ -394,7 +397,58 @@ class _PackedGenerator:
                        "bvg_forward_cond")
         return wav
 
+    # ---- CUDA-graph replay for small, launch-bound calls (one 5 s utterance is 214 launches in ~2 ms) -----------------
+    # Off unless BigVGAN.set_cuda_graphs(max_frames) / $BVG_GRAPH_MAX_FRAMES says otherwise.  A call with B*T <= max_frames
+    # is captured once per (B, T, output dtype) into a graph with static input / output / workspace buffers and replayed
+    # afterwards: copy in, one graph launch, copy out.  The cache is per host thread (two server threads never share static
+    # buffers); an event orders reuse of the buffers across streams of one thread.  Results are bit-identical to the eager
+    # plan (same kernels, same order).
+    GRAPH_CACHE_ENTRIES = 4
+
+    def _graphs(self):
+        tl = self.__dict__.setdefault("_tl", threading.local())
+        if not hasattr(tl, "graphs"):
+            tl.graphs = collections.OrderedDict()
+        return tl.graphs
+
+    def _run_graphed(self, mel: torch.Tensor, pcm16: bool) -> torch.Tensor:
+        cache = self._graphs()
+        key = (tuple(mel.shape), bool(pcm16), mel.device)
+        ent = cache.get(key)
+        cur = torch.cuda.current_stream(mel.device)
+        if ent is None:
+            static_in = torch.empty(tuple(mel.shape), dtype=torch.float32, device=mel.device)
+            static_in.copy_(mel)
+            self._run_eager(static_in, pcm16)  # warm-up outside capture (lazy CUDA state, aux streams of the library)
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                static_out = self._run_eager(static_in, pcm16)
+            ent = [g, static_in, static_out, None]
+            cache[key] = ent
+            while len(cache) > self.GRAPH_CACHE_ENTRIES:
+                cache.popitem(last=False)
+        else:
+            cache.move_to_end(key)
+            if ent[3] is not None:
+                cur.wait_event(ent[3])
+        g, static_in, static_out, _ = ent
+        static_in.copy_(mel)
+        g.replay()
+        out = static_out.clone()
+        ev = torch.cuda.Event()
+        ev.record(cur)
+        ent[3] = ev
+        return out
+
     def run(self, mel: torch.Tensor, pcm16: bool = False) -> torch.Tensor:
+        B, _, T = mel.shape
+        if (self.graph_max_frames > 0 and 0 < B * T <= self.graph_max_frames
+                and not torch.cuda.is_current_stream_capturing()):
+            with torch.cuda.device(mel.device):
+                return self._run_graphed(mel, pcm16)
+        return self._run_eager(mel, pcm16)
+
+    def _run_eager(self, mel: torch.Tensor, pcm16: bool = False) -> torch.Tensor:
         lib = _lib.load()
         B, _, T = mel.shape
         wav = torch.empty((B, 1, T * self.hop), dtype=torch.int16 if pcm16 else torch.float32, device=mel.device)
@@ -486,6 +540,16 @@ class _GeneratorPlanMixin:
         self.__dict__["_bvg_precision"] = DEFAULT_PRECISION
         self.__dict__["_bvg_plan"] = None
         self.__dict__["_bvg_plan_key"] = None
+        self.__dict__["_bvg_graph_max_frames"] = int(os.environ.get("BVG_GRAPH_MAX_FRAMES", "0") or 0)
+
+    def set_cuda_graphs(self, max_frames: int):
+        """Extra (not in the reference): replay calls with ``B * T_mel <= max_frames`` from CUDA graphs (one graph per
+        input shape and host thread, captured on first use; 0 switches it off).  For launch-bound single-utterance
+        calls such as ``infer_v2.py:860`` (B = 1); bit-identical results."""
+        self.__dict__["_bvg_graph_max_frames"] = int(max_frames)
+        if self.__dict__["_bvg_plan"] is not None:
+            self.__dict__["_bvg_plan"].graph_max_frames = int(max_frames)
+        return self
 
     def set_precision(self, precision: str):
         ops.precision_code(precision)

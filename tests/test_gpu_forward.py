@@ -256,3 +256,58 @@ def test_torch_compile_dynamic(full_models):
             x = torch.randn(1, 80, T, generator=torch.Generator().manual_seed(T)).cuda()
             assert torch.equal(cm(x), m(x))
     m.set_precision("fp32")
+
+
+def test_cuda_graph_replay_cache_is_bit_identical(full_models):
+    """``set_cuda_graphs``: small calls replayed from per-shape, per-thread CUDA graphs equal the eager plan bit for bit --
+    repeated shapes, more shapes than cache entries, a strided mel, a side stream, two host threads, PCM output."""
+    import threading
+    sd, m = full_models
+    m.set_precision("bf16")
+    gens = [torch.Generator().manual_seed(70 + i) for i in range(7)]
+    mels = [torch.randn(1 + (i % 2), 80, 24 + 5 * i, generator=gens[i]).cuda() for i in range(7)]
+    with torch.no_grad():
+        want = [m(x).clone() for x in mels]
+        want_pcm = m.forward_pcm16(mels[0]).clone()
+        m.set_cuda_graphs(4096)
+        try:
+            for rep in range(3):
+                for i, x in enumerate(mels):  # 7 shapes > 4 cache entries: eviction and re-capture
+                    assert torch.equal(m(x), want[i]), (rep, i)
+            assert torch.equal(m.forward_pcm16(mels[0]), want_pcm)
+            wide = torch.randn(1, 80, 60, generator=gens[0]).cuda()
+            view = wide[:, :, 11:11 + mels[0].shape[2]]
+            assert not view.is_contiguous()
+            assert torch.equal(m(view), m.set_cuda_graphs(0)(view.contiguous()))
+            m.set_cuda_graphs(4096)
+            s = torch.cuda.Stream()
+            with torch.cuda.stream(s):
+                a = m(mels[2])
+                b = m(mels[2])
+            c = m(mels[2])  # same graph from another stream of the same thread
+            torch.cuda.synchronize()
+            assert torch.equal(a, want[2]) and torch.equal(b, want[2]) and torch.equal(c, want[2])
+            big = torch.randn(4, 80, 2000, generator=gens[1]).cuda()  # above the threshold: eager path
+            assert m(big).shape == (4, 1, 2000 * 256)
+            errs, out = [], {}
+
+            def worker(tid):
+                try:
+                    st = torch.cuda.Stream()
+                    with torch.cuda.stream(st), torch.no_grad():
+                        for rep in range(4):
+                            for i in range(tid, 4, 2):
+                                out[(tid, rep, i)] = m(mels[i])
+                    st.synchronize()
+                except Exception as e:  # pragma: no cover
+                    errs.append(e)
+
+            ts = [threading.Thread(target=worker, args=(t,)) for t in range(2)]
+            [t.start() for t in ts]
+            [t.join() for t in ts]
+            assert not errs, errs
+            for (tid, rep, i), y in out.items():
+                assert torch.equal(y, want[i]), (tid, rep, i)
+        finally:
+            m.set_cuda_graphs(0)
+            m.set_precision("fp32")
