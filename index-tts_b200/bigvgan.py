@@ -421,7 +421,9 @@ class _PackedGenerator:
             static_in.copy_(mel)
             self._run_eager(static_in, pcm16)  # warm-up outside capture (lazy CUDA state, aux streams of the library)
             g = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(g):
+            # thread_local: other host threads keep launching / allocating while this one captures (serve_tars.py's
+            # two workers); the default global mode would fail THEIR calls with cudaErrorIllegalState
+            with torch.cuda.graph(g, capture_error_mode="thread_local"):
                 static_out = self._run_eager(static_in, pcm16)
             ent = [g, static_in, static_out, None]
             cache[key] = ent
