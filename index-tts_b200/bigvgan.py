@@ -423,7 +423,8 @@ class _PackedGenerator:
             g = torch.cuda.CUDAGraph()
             # thread_local: other host threads keep launching / allocating while this one captures (serve_tars.py's
             # two workers); the default global mode would fail THEIR calls with cudaErrorIllegalState
-            with torch.cuda.graph(g, capture_error_mode="thread_local"):
+            # own capture stream: torch.cuda.graph's default one is shared by all threads of the process
+            with torch.cuda.graph(g, stream=torch.cuda.Stream(mel.device), capture_error_mode="thread_local"):
                 static_out = self._run_eager(static_in, pcm16)
             ent = [g, static_in, static_out, None]
             cache[key] = ent

@@ -299,13 +299,14 @@ def test_cuda_graph_replay_cache_is_bit_identical(full_models):
                             for i in range(tid, 4, 2):
                                 out[(tid, rep, i)] = m(mels[i])
                     st.synchronize()
-                except Exception as e:  # pragma: no cover
-                    errs.append(e)
+                except Exception:  # pragma: no cover
+                    import traceback
+                    errs.append(traceback.format_exc())
 
             ts = [threading.Thread(target=worker, args=(t,)) for t in range(2)]
             [t.start() for t in ts]
             [t.join() for t in ts]
-            assert not errs, errs
+            assert not errs, "\n".join(errs)
             for (tid, rep, i), y in out.items():
                 assert torch.equal(y, want[i]), (tid, rep, i)
         finally:
