@@ -233,6 +233,7 @@ class AMPBlock2(torch.nn.Module):
 # whole-generator launch plan
 # ---------------------------------------------------------------------------------------------------------------
 _PLANS: "weakref.WeakValueDictionary[int, _PackedGenerator]" = weakref.WeakValueDictionary()
+_CAPTURE_LOCK = threading.Lock()
 _next_plan_id = [1]
 
 
@@ -421,11 +422,14 @@ class _PackedGenerator:
             static_in.copy_(mel)
             self._run_eager(static_in, pcm16)  # warm-up outside capture (lazy CUDA state, aux streams of the library)
             g = torch.cuda.CUDAGraph()
-            # thread_local: other host threads keep launching / allocating while this one captures (serve_tars.py's
-            # two workers); the default global mode would fail THEIR calls with cudaErrorIllegalState
-            # own capture stream: torch.cuda.graph's default one is shared by all threads of the process
-            with torch.cuda.graph(g, stream=torch.cuda.Stream(mel.device), capture_error_mode="thread_local"):
-                static_out = self._run_eager(static_in, pcm16)
+            # One capture at a time in the process (_CAPTURE_LOCK): two simultaneous captures were seen to invalidate each
+            # other.  thread_local error mode: other host threads keep launching / allocating while this one captures
+            # (serve_tars.py's two workers); the default global mode would fail THEIR calls with cudaErrorIllegalState.
+            # Own capture stream: torch.cuda.graph's default one is shared by all threads of the process.
+            with _CAPTURE_LOCK:
+                cur.synchronize()
+                with torch.cuda.graph(g, stream=torch.cuda.Stream(mel.device), capture_error_mode="thread_local"):
+                    static_out = self._run_eager(static_in, pcm16)
             ent = [g, static_in, static_out, None]
             cache[key] = ent
             while len(cache) > self.GRAPH_CACHE_ENTRIES:
