@@ -489,6 +489,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                         }
                     }
                 }
+#ifndef BVG_NO_COND  // developer A/B only (tools/build_variant.sh): the epilogue without the conditioning branch
                 if (p.cond) {  // warp-uniform addresses: one broadcast transaction per float4
                     const int chb = c0 + c;
                     const float* cv = p.cond + static_cast<size_t>(b) * p.cout_phase + chb;
@@ -500,6 +501,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                         }
                     }
                 }
+#endif
                 if (n_ld > 0) {
                     mbar_wait_warp(&ld_full[ls], pls);
                     const uint8_t* ld = sLdG + ls * n_ld * EPI_LD_TILE_BYTES + row * 128;
