@@ -338,11 +338,20 @@ def main():
             ms_v1 = timed(fv, 3)
             fd()
             ms_v1d = timed(fd, 3)
+        for _ in range(2):
+            mv.profile_with_embedding(xv, embv)
+        _, recs_v1 = mv.profile_with_embedding(xv, embv)
+        peaks_v = load_peaks()
+        roof_v1 = sum(max(r["flops"] / (peaks_v["tf_sus"] * 1e12), r["bytes"] / (peaks_v["hbm"] * 1e9)) * 1e3
+                      for r in recs_v1 if r["kind"] != "layout")
+        meas_v1 = sum(r["ms"] for r in recs_v1 if r["kind"] != "layout")
         audio_v1 = Bsz * Tv * 1024 / 24000.0
         v1_line = {"workload": "v1 generator (models.py shape class: 1536 ch, rates 4,4,4,4,2,2, gpt_dim 1024, D 512), "
                                f"batch {Bsz} x {Tv} latent frames (10 s each), random-init, {args.precision}",
                    "value": audio_v1 / (ms_v1 * 1e-3), "unit": "audio-s/s", "ms_per_step": ms_v1,
-                   "decoder_only_ms": ms_v1d, "decoder_only_value": audio_v1 / (ms_v1d * 1e-3)}
+                   "decoder_only_ms": ms_v1d, "decoder_only_value": audio_v1 / (ms_v1d * 1e-3),
+                   "per_layer_roofline": {"roofline_ms": roof_v1, "measured_ms": meas_v1,
+                                          "frac": roof_v1 / meas_v1 if meas_v1 > 0 else None, "launches": len(recs_v1)}}
         del mv, xv, melv
 
     # ---- single-utterance latency (BASELINE.json configs[0] shape: one 5 s mel, 80x431; the reference pipeline calls the

@@ -250,6 +250,12 @@ BVG_API int bvg_forward_profile(const bvg_model_desc* m_host, const float* mel, 
                         float* wav, int64_t B, int64_t T_mel, void* workspace, size_t workspace_bytes, void* stream,
                         bvg_launch_record* records_host, int max_records, int* n_records);
 
+/* the same for bvg_forward_cond (v1 generator) */
+BVG_API int bvg_forward_cond_profile(const bvg_model_desc* m_host, const float* x, int x_layout, int64_t x_stride_b,
+                             int64_t x_stride_c, const float* const* cond_host, float* wav, int64_t B, int64_t T,
+                             void* workspace, size_t workspace_bytes, void* stream, bvg_launch_record* records_host,
+                             int max_records, int* n_records);
+
 /* Developer instrumentation (no reference counterpart): when `buf` is a device buffer of 16 * n_tiles uint64 the next
  * tcgen05 conv launches record SM cycle counters of CTA 0's pipeline roles (TMA producer / UMMA issuer / epilogue) for
  * their first n_tiles tiles (tools/conv_timeline.py).  Pass NULL to switch it off (the default). */

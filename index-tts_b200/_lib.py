@@ -86,6 +86,8 @@ SIGNATURES = {
     "bvg_forward": (c_int, [C.POINTER(ModelDesc), c_vp, c_i64, c_i64, c_vp, c_i64, c_i64, c_vp, c_sz, c_vp]),
     "bvg_forward_profile": (c_int, [C.POINTER(ModelDesc), c_vp, c_i64, c_i64, c_vp, c_i64, c_i64, c_vp, c_sz, c_vp,
                                     C.POINTER(LaunchRecord), c_int, C.POINTER(c_int)]),
+    "bvg_forward_cond_profile": (c_int, [C.POINTER(ModelDesc), c_vp, c_int, c_i64, c_i64, C.POINTER(c_vp), c_vp, c_i64, c_i64,
+                                         c_vp, c_sz, c_vp, C.POINTER(LaunchRecord), c_int, C.POINTER(c_int)]),
     "bvg_debug_conv_trace": (None, [c_vp, c_int]),
     "bvg_cond_linear_fwd": (c_int, [c_vp, c_vp, c_vp, c_vp, c_i64, c_i64, c_i64, c_vp]),
     "bvg_add_channel_vector_nlc": (c_int, [c_vp, c_int, c_vp, c_vp, c_int, c_i64, c_i64, c_i64, c_vp]),

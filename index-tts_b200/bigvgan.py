@@ -500,6 +500,29 @@ def profile_forward(model: "BigVGAN", mel: torch.Tensor):
     return wav, out
 
 
+def profile_forward_cond(plan: _PackedGenerator, x_nlc: torch.Tensor, conds):
+    """``profile_forward`` for the v1 generator (``bvg_forward_cond_profile``): ``x_nlc`` fp32 ``[B, T, gpt_dim]``,
+    ``conds`` as in ``_PackedGenerator.run_cond``.  Returns ``(wav, records)``."""
+    lib = _lib.load()
+    B, T, _ = x_nlc.shape
+    x_nlc = x_nlc.float().contiguous()
+    wav = torch.empty((B, 1, T * plan.hop), dtype=torch.float32, device=x_nlc.device)
+    n_c = plan.desc.num_stages + 1
+    conds = [None if c is None or c.numel() == 0 else c.detach().float().contiguous() for c in conds]
+    arr = (ctypes.c_void_p * n_c)(*[None if c is None else c.data_ptr() for c in conds])
+    ws_bytes = lib.bvg_workspace_bytes(ctypes.byref(plan.desc), B, T)
+    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=x_nlc.device)
+    recs = (_lib.LaunchRecord * 1024)()
+    n = ctypes.c_int(0)
+    with torch.cuda.device(x_nlc.device):
+        _lib.check(lib.bvg_forward_cond_profile(ctypes.byref(plan.desc), x_nlc.data_ptr(), 1, 0, 0, arr, wav.data_ptr(), B, T,
+                                                ws.data_ptr(), ws_bytes, torch.cuda.current_stream().cuda_stream, recs,
+                                                1024, ctypes.byref(n)), "bvg_forward_cond_profile")
+    out = [dict(kind=_lib.KIND_NAMES.get(r.kind, str(r.kind)), stage=r.stage, cin=r.cin, cout=r.cout, k=r.k,
+                dilation=r.dilation, rows=r.rows, flops=r.flops, bytes=r.bytes, ms=r.ms) for r in recs[:min(n.value, 1024)]]
+    return wav, out
+
+
 @torch.library.custom_op("bvg::vocoder_forward", mutates_args=())
 def _vocoder_forward(mel: torch.Tensor, plan_id: int, hop: int) -> torch.Tensor:
     plan = _PLANS.get(plan_id)

@@ -445,11 +445,20 @@ extern "C" int bvg_forward_pcm16(const bvg_model_desc* m, const float* mel, int6
 extern "C" int bvg_forward_profile(const bvg_model_desc* m, const float* mel, int64_t mel_stride_b, int64_t mel_stride_c,
                                    float* wav, int64_t B, int64_t T_mel, void* workspace, size_t workspace_bytes,
                                    void* stream, bvg_launch_record* records_host, int max_records, int* n_records) {
+    return bvg_forward_cond_profile(m, mel, 0, mel_stride_b, mel_stride_c, nullptr, wav, B, T_mel, workspace, workspace_bytes,
+                                    stream, records_host, max_records, n_records);
+}
+
+extern "C" int bvg_forward_cond_profile(const bvg_model_desc* m, const float* mel, int x_layout, int64_t mel_stride_b,
+                                        int64_t mel_stride_c, const float* const* cond_host, float* wav, int64_t B,
+                                        int64_t T_mel, void* workspace, size_t workspace_bytes, void* stream,
+                                        bvg_launch_record* records_host, int max_records, int* n_records) {
     BVG_REQUIRE(records_host && n_records && max_records >= 0, BVG_ERR_INVALID, "bvg_forward_profile: null record buffer");
     std::vector<ProfEntry> entries;
     entries.reserve(512);
     g_prof = &entries;
-    const int rc = bvg_forward(m, mel, mel_stride_b, mel_stride_c, wav, B, T_mel, workspace, workspace_bytes, stream);
+    const int rc = forward_impl(m, mel, x_layout, mel_stride_b, mel_stride_c, cond_host, wav, BVG_F32, B, T_mel, workspace,
+                                workspace_bytes, stream);
     g_prof = nullptr;
     cudaError_t e = cudaStreamSynchronize(static_cast<cudaStream_t>(stream));
     int n = 0;

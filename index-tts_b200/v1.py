@@ -135,11 +135,21 @@ class BigVGAN(_GeneratorPlanMixin, torch.nn.Module):
             x = torch.nn.functional.interpolate(x.transpose(1, 2), scale_factor=[4], mode="linear").transpose(1, 2)
         x = x.float().contiguous()
         plan = self._plan(x.device)
-        empty = x.new_empty(0)
+        return _vocoder_forward_cond(x, self._cond_vectors(e, x), plan.plan_id, plan.hop)
+
+    def _cond_vectors(self, e, like):
         conds = [ops.cond_linear(e, self.cond_layer.weight, self.cond_layer.bias)]
         for i in range(self.num_upsamples):
-            conds.append(ops.cond_linear(e, self.conds[i].weight, self.conds[i].bias) if self.cond_in_each_up_layer else empty)
-        return _vocoder_forward_cond(x, conds, plan.plan_id, plan.hop)
+            conds.append(ops.cond_linear(e, self.conds[i].weight, self.conds[i].bias) if self.cond_in_each_up_layer
+                         else like.new_empty(0))
+        return conds
+
+    def profile_with_embedding(self, x, speaker_embedding):
+        """Measurement helper (bench.py): ``forward_with_embedding`` with a CUDA event pair around every launch."""
+        from .bigvgan import profile_forward_cond
+        x = x.float().contiguous()
+        e = speaker_embedding.reshape(speaker_embedding.shape[0], -1).float()
+        return profile_forward_cond(self._plan(x.device), x, self._cond_vectors(e, x))
 
     def forward(self, x, mel_ref, lens=None):
         """``x`` ``[B, T, gpt_dim]``, ``mel_ref`` ``[B, T_ref, num_mels]`` -> ``(wav [B, 1, T * hop], None)``
