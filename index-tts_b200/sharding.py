@@ -144,16 +144,21 @@ def forward_time_sharded(forward_fn: Callable[[torch.Tensor], torch.Tensor], mel
     return None
 
 
-def forward_batch_sharded(forward_fn: Callable[[torch.Tensor], torch.Tensor], mels: Sequence[torch.Tensor], hop: int,
-                          dst: Optional[int] = None, group=None) -> List[Optional[torch.Tensor]]:
+def forward_batch_sharded(forward_fn: Callable, mels: Sequence[torch.Tensor], hop: int,
+                          dst: Optional[int] = None, group=None, time_dim: int = -1,
+                          indexed: bool = False) -> List[Optional[torch.Tensor]]:
     """Utterance-parallel vocoding of a ragged list of mels ``[num_mels, T_b]`` (every rank holds the list; each mel
     is a few hundred KB).  Rank ``b mod world`` vocodes utterance b.  With ``dst=None`` each rank keeps its own
-    results (entries it does not own are None); otherwise the waveforms are P2P-sent to ``dst``."""
+    results (entries it does not own are None); otherwise the waveforms are P2P-sent to ``dst``.
+
+    v1 generator: the items are channels-last latents ``[T_b, gpt_dim]`` (``time_dim=0``) and every utterance has its own
+    speaker embedding, so ``indexed=True`` calls ``forward_fn(b, x)`` with the utterance index."""
     rank, world = _rank_world(group)
     owners = split_batch(len(mels), world)
     out: List[Optional[torch.Tensor]] = [None] * len(mels)
     for b in owners[rank]:
-        out[b] = forward_fn(mels[b].unsqueeze(0))[0]
+        xb = mels[b].unsqueeze(0)
+        out[b] = (forward_fn(b, xb) if indexed else forward_fn(xb))[0]
     if dst is None or world == 1:
         return out
     if rank == dst:
@@ -162,7 +167,7 @@ def forward_batch_sharded(forward_fn: Callable[[torch.Tensor], torch.Tensor], me
             if r == dst:
                 continue
             for b in owners[r]:
-                out[b] = torch.empty((1, mels[b].shape[-1] * hop), dtype=torch.float32, device=mels[b].device)
+                out[b] = torch.empty((1, mels[b].shape[time_dim] * hop), dtype=torch.float32, device=mels[b].device)
                 reqs.append(dist.irecv(out[b], _global_rank(group, r), group=group))
         for q in reqs:
             q.wait()

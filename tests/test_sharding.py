@@ -80,6 +80,19 @@ def _worker(rank, world, port, scatter, q):
             owner = 0
         mels = [torch.from_numpy(rng.standard_normal((80, t)).astype(np.float32)) for t in (7, 12, 9)]
         wavs = S.forward_batch_sharded(fn, mels, HOP, dst=0)
+        # v1 generator: channels-last latents, one speaker embedding per utterance (forward_fn gets the index)
+        hv = dict(O.V1_HPARAMS, upsample_initial_channel=64, gpt_dim=16, speaker_embedding_dim=8, upsample_rates=[4, 2],
+                  upsample_kernel_sizes=[8, 4], resblock_kernel_sizes=[3], resblock_dilation_sizes=[[1, 3]])
+        sdv = O.make_state_dict(hv, seed=4)
+        lat = [torch.from_numpy(rng.standard_normal((t, 16)).astype(np.float32)) for t in (5, 8, 6)]
+        emb = rng.standard_normal((3, 8)).astype(np.float32)
+        fnv = lambda b, x: torch.from_numpy(O.forward_v1(sdv, x.numpy(), emb[b:b + 1], hv, np.float32))
+        wv = S.forward_batch_sharded(fnv, lat, 8, dst=0, time_dim=0, indexed=True)
+        if rank == 0:
+            errv = max(float((w - fnv(b, x.unsqueeze(0))[0]).abs().max()) for b, (w, x) in enumerate(zip(wv, lat)))
+            assert errv <= 1e-6 and tuple(w.shape[-1] for w in wv) == (40, 64, 48), (errv, [w.shape for w in wv])
+        else:
+            assert wv == [None] * 3
         if rank == owner:
             q.put(("time", float((out - fn(mel)).abs().max()), tuple(out.shape)))
         else:
