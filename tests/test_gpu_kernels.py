@@ -330,3 +330,18 @@ def test_conv1d_tcgen05_bf16_long(ops, case):
                                   out_f32=True, out_bf16=True)
         assert rel_err(ref, y32.cpu().numpy()) < 2e-5
         assert rel_err(ref, y16.float().cpu().numpy()) < 2.0 ** -8
+
+
+def test_activation1d_fast_path_far_outside_init_range(ops):
+    """snake parameters of a trained checkpoint are not N(0, 0.5).  alpha_log / beta_log uniform in
+    +-3 (a up to 20) and 4x inputs (arguments up to ~750 rad): the MUFU path must stay an fp32-grade result
+    (profiles/r01_v8_act_range_probe.log: 120.9 dB measured, the range-reduced path 124.1 dB)."""
+    rng = np.random.default_rng(5)
+    C, T = 48, 4096
+    x = (rng.standard_normal((2, C, T)) * 4.0).astype(np.float32)
+    al = rng.uniform(-3, 3, C).astype(np.float32)
+    be = rng.uniform(-3, 3, C).astype(np.float32)
+    ref = O.activation1d(x.astype(np.float64), al, be)
+    for precise in (False, True):
+        y = ops.activation1d(_t(x), _t(al), _t(be), precise).cpu().numpy()
+        assert snr_db(ref, y) > 110.0, (precise, snr_db(ref, y))
