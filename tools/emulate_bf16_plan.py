@@ -15,7 +15,7 @@ from oracle import bigvgan_oracle as O
 def r16(x):
     return x.to(torch.bfloat16).to(torch.float32)
 
-def run(ref, mel, y1_bf16, pre_bf16=True):
+def run(ref, mel, y1_bf16, pre_bf16=True, res16_from_stage=99, x16_from_stage=99):
     h = ref.h
     nk = ref.num_kernels
     with torch.no_grad():
@@ -26,7 +26,7 @@ def run(ref, mel, y1_bf16, pre_bf16=True):
             xs = None
             for j in range(nk):
                 rb = ref.resblocks[i * nk + j]
-                xr = x
+                xr = r16(x) if i >= x16_from_stage else x
                 for l in range(3):
                     a1, a2 = rb.activations[2 * l], rb.activations[2 * l + 1]
                     c1, c2 = rb.convs1[l], rb.convs2[l]
@@ -37,6 +37,8 @@ def run(ref, mel, y1_bf16, pre_bf16=True):
                     xt = r16(a2(xt))
                     xt = F.conv1d(xt, r16(c2.weight), c2.bias, padding=c2.padding)
                     xr = xt + xr
+                    if i >= res16_from_stage and l < 2:  # inter-layer residual stream of the block stored as bf16
+                        xr = r16(xr)
                 xs = xr if xs is None else xs + xr
             x = xs / nk
         x = ref.activation_post(x)
@@ -65,3 +67,7 @@ if __name__ == "__main__":
         for y1 in (False, True):
             w = run(ref, mel, y1)
             print(f"seed {seed} T {T} y1_bf16={y1}: SNR {O.snr_db(w32.numpy(), w.numpy()):.2f} dB, max-abs {float((w-w32).abs().max()):.2e}", flush=True)
+        # bf16 storage of the blocks' inter-layer residual stream (res16) / of the stage input X (x16) from a given stage on
+        for rs, xs_ in ((3, 99), (0, 99), (3, 3), (0, 0)):
+            w = run(ref, mel, True, res16_from_stage=rs, x16_from_stage=xs_)
+            print(f"seed {seed} T {T} res16>={rs} x16>={xs_}: SNR {O.snr_db(w32.numpy(), w.numpy()):.2f} dB", flush=True)
