@@ -182,3 +182,29 @@ def test_gpu_v1_unfused_conditioning_path_matches_too(golden_dir):
     env = dict(os.environ, BVG_COND_FUSED="0")
     out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300, env=env)
     assert out.returncode == 0 and out.stdout.strip().endswith("ok"), out.stderr[-2000:]
+
+
+@pytest.mark.gpu
+def test_gpu_v1_edge_shapes():
+    """Empty batch, empty time axis, a single latent frame (every conv sees only padding around it), fp32 and bf16."""
+    h = dict(V1_MINI_H)
+    sd = O.make_state_dict(h, seed=33)
+    m = _build_v1(h, sd, "fp32")
+    D, E = h["gpt_dim"], h["speaker_embedding_dim"]
+    with torch.no_grad():
+        assert m.forward_with_embedding(torch.zeros(0, 5, D).cuda(), torch.zeros(0, E).cuda()).shape == (0, 1, 5 * 1024)
+        assert m.forward_with_embedding(torch.zeros(2, 0, D).cuda(), torch.zeros(2, E).cuda()).shape == (2, 1, 0)
+        rng = np.random.default_rng(2)
+        x = rng.standard_normal((2, 1, D)).astype(np.float32)
+        e = rng.standard_normal((2, E)).astype(np.float32)
+        ref = O.forward_v1(sd, x, e, h, np.float64)
+        w = m.forward_with_embedding(torch.from_numpy(x).cuda(), torch.from_numpy(e).cuda()).cpu().numpy()
+        assert w.shape == ref.shape == (2, 1, 1024)
+        assert np.abs(w - ref).max() <= 1e-4 and O.snr_db(ref, w) >= 80.0
+        m.set_precision("bf16")
+        w16 = m.forward_with_embedding(torch.from_numpy(x).cuda(), torch.from_numpy(e).cuda()).cpu().numpy()
+        assert O.snr_db(ref, w16) >= 40.0
+        with pytest.raises(ValueError):
+            m.forward_with_embedding(torch.zeros(2, 3, D + 8).cuda(), torch.zeros(2, E).cuda())
+        with pytest.raises(ValueError):
+            m.forward_with_embedding(torch.zeros(2, 3, D).cuda(), torch.zeros(3, E).cuda())
