@@ -126,7 +126,7 @@ class BigVGAN(_GeneratorPlanMixin, torch.nn.Module):
             raise _lib.BvgError("BigVGAN.forward: libbvg has no CPU path; move the module and the inputs to a B200 "
                                 f"(got device {x.device})")
         _lib.require_device(x.device.index if x.device.index is not None else torch.cuda.current_device())
-        e = speaker_embedding.reshape(speaker_embedding.shape[0], -1).float()
+        e = speaker_embedding.reshape(speaker_embedding.shape[0], self.cond_layer.in_channels).float()
         if e.shape[0] != x.shape[0]:
             raise ValueError(f"{e.shape[0]} speaker embeddings for a batch of {x.shape[0]}")
         if self.feat_upsample:
@@ -148,7 +148,7 @@ class BigVGAN(_GeneratorPlanMixin, torch.nn.Module):
         """Measurement helper (bench.py): ``forward_with_embedding`` with a CUDA event pair around every launch."""
         from .bigvgan import profile_forward_cond
         x = x.float().contiguous()
-        e = speaker_embedding.reshape(speaker_embedding.shape[0], -1).float()
+        e = speaker_embedding.reshape(speaker_embedding.shape[0], self.cond_layer.in_channels).float()
         return profile_forward_cond(self._plan(x.device), x, self._cond_vectors(e, x))
 
     def forward(self, x, mel_ref, lens=None):
