@@ -82,10 +82,10 @@ static int launch_add(const void* x, const float* v, void* y, int64_t B, int64_t
 
 int add_channel_vector(const void* x, int x_dtype, const float* v, void* y, int y_dtype, int64_t B, int64_t T, int64_t C,
                        cudaStream_t st) {
-    BVG_REQUIRE(x && y, BVG_ERR_INVALID, "add_channel_vector: null pointer");
     BVG_REQUIRE(B >= 0 && T >= 0 && C > 0 && C % 4 == 0 && B < 65536, BVG_ERR_UNSUPPORTED,
                 "add_channel_vector: need C %% 4 == 0 and B < 65536 (B=%lld C=%lld)", (long long)B, (long long)C);
     if (B == 0 || T == 0) return BVG_OK;
+    BVG_REQUIRE(x && y, BVG_ERR_INVALID, "add_channel_vector: null pointer");
     if (x_dtype == BVG_F32 && y_dtype == BVG_F32) return launch_add<float, float>(x, v, y, B, T, C, st);
     if (x_dtype == BVG_F32 && y_dtype == BVG_BF16) return launch_add<float, __nv_bfloat16>(x, v, y, B, T, C, st);
     if (x_dtype == BVG_BF16 && y_dtype == BVG_BF16) return launch_add<__nv_bfloat16, __nv_bfloat16>(x, v, y, B, T, C, st);
@@ -99,9 +99,9 @@ using namespace bvg;
 
 extern "C" int bvg_cond_linear_fwd(const float* e, const float* w, const float* bias, float* y, int64_t B, int64_t D,
                                    int64_t C, void* stream) {
-    BVG_REQUIRE(e && w && y, BVG_ERR_INVALID, "bvg_cond_linear_fwd: null pointer");
     BVG_REQUIRE(B >= 0 && D > 0 && C > 0 && B * C < (int64_t(1) << 31) / 32, BVG_ERR_INVALID, "bvg_cond_linear_fwd: bad shape");
-    if (B == 0) return BVG_OK;
+    if (B == 0) return BVG_OK;  // an empty batch has no storage behind its pointers
+    BVG_REQUIRE(e && w && y, BVG_ERR_INVALID, "bvg_cond_linear_fwd: null pointer");
     const unsigned grid = (unsigned)ceil_div(B * C * 32, 256);
     cond_linear_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(e, w, bias, y, B, D, C);
     BVG_LAUNCH_CHECK("cond_linear_kernel");
