@@ -47,6 +47,7 @@ constexpr int EPI_ST16_TILE_BYTES = 32 * 64;   // per-warp bf16 output chunk: 32
 struct ConvUmmaParams {
     const float* bias;      // [cout_phase] or null
     const float* cond;      // per-utterance bias [B, cout_phase] or null (v1 generator conditioning)
+    int cluster;            // 1: clusters of two CTAs share every streamed weight stage by TMA multicast (see launcher)
     const float* residual;  // [B,T,N] fp32 or null
     const float* accum;     // [B,T,N] fp32 or null
     float* y_f32;           // [B,T,N] or null
@@ -157,7 +158,7 @@ template <bool STAT>
 __device__ __forceinline__ void umma_issue_loop(const ConvUmmaParams& p, uint32_t tmem_base, uint32_t sA_d, uint32_t sB_d,
                                                 uint64_t* a_full, uint64_t* a_empty, uint64_t* b_full, uint64_t* b_empty,
                                                 uint64_t* acc_full, uint64_t* acc_empty, int k_blocks, int n_tiles,
-                                                int group) {
+                                                int group, uint32_t cta_first, uint32_t cta_step) {
     const uint32_t idesc = umma_idesc_bf16_f32(UMMA_BLOCK_M, p.n_tile);
     const uint32_t desc_hi = static_cast<uint32_t>(umma_desc_sw128_kmajor(0) >> 32);
     const uint32_t tap_step = static_cast<uint32_t>(p.dil) * 8u;  // dil rows * 128 B >> 4
@@ -183,7 +184,8 @@ __device__ __forceinline__ void umma_issue_loop(const ConvUmmaParams& p, uint32_
     uint32_t acc = 0, pa = 0, pb = 0, pacc = 0;
     if (STAT) mbar_wait_warp(&b_full[0], 0);
     uint32_t it = 0;
-    for (uint32_t tile = blockIdx.x + group * gridDim.x; tile < total; tile += ng * gridDim.x, ++it) {
+    const bool cluster = p.cluster != 0;
+    for (uint32_t tile = cta_first + group * cta_step; tile < total; tile += ng * cta_step, ++it) {
         mbar_wait_warp(&acc_empty[acc], pacc ^ 1);
         tc_fence_after_sync();
         if (leader) trace_ev(p, 1 + 6 * group, it);
@@ -221,7 +223,10 @@ __device__ __forceinline__ void umma_issue_loop(const ConvUmmaParams& p, uint32_
                         if (k3) umma_f16_lo(d2, a2 + 4, b_d + 4, desc_hi, idesc, 1);
                         if (k4) umma_f16_lo(d2, a2 + 6, b_d + 6, desc_hi, idesc, 1);
                     }
-                    if (!STAT) umma_commit(&b_empty[sb]);
+                    if (!STAT) {
+                        if (cluster) umma_commit_mc(&b_empty[sb], 3);  // both CTAs refill this slot together
+                        else umma_commit(&b_empty[sb]);
+                    }
                 }
                 accumulate = 1;
                 a_d += tap_step;
@@ -283,7 +288,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
         tma_prefetch_desc(&map_w);
         for (int i = 0; i < UMMA_MAX_STAGES; ++i) {
             mbar_init(&a_full[i], 1); mbar_init(&a_empty[i], 1);
-            mbar_init(&b_full[i], 1); mbar_init(&b_empty[i], 1);
+            mbar_init(&b_full[i], 1); mbar_init(&b_empty[i], p.cluster ? 2 : 1);
             mbar_init(&ld_full[i], 1); mbar_init(&ld_empty[i], 4);
         }
         for (int i = 0; i < 4; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 4); }
@@ -297,12 +302,20 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
     tc_fence_before_sync();
     __syncthreads();
     tc_fence_after_sync();
+    if (p.cluster) cluster_sync_all();  // the peer's barriers exist before any multicast / remote arrive targets them
     const uint32_t tmem_base = *tmem_ptr;
 
     const int k_blocks = (p.Cin + UMMA_BLOCK_K - 1) / UMMA_BLOCK_K;
     const int n_tiles = p.num_phases * p.tiles_per_phase;
     const uint32_t total_tiles = static_cast<uint32_t>(p.total_tiles);
     const uint32_t m_tiles = static_cast<uint32_t>(p.m_tiles);
+    // Cluster mode: the tile index space is one of row-tile PAIRS (p.m_tiles = pairs, set by the launcher); the two CTAs
+    // of a cluster walk the same pairs and take row tile 2 * pair + rank, so they need the same weight stages in the
+    // same order.  An odd row-tile count leaves a ghost tile past T: its loads are zero-filled, its stores clipped.
+    const uint32_t crank = p.cluster ? (blockIdx.x & 1u) : 0u;
+    const uint32_t cta_first = p.cluster ? (blockIdx.x >> 1) : blockIdx.x;
+    const uint32_t cta_step = p.cluster ? (gridDim.x >> 1) : gridDim.x;
+    const int mt_mul = p.cluster ? 2 : 1;
 
     if (warp == 0) {
         // ------------------------------ TMA producer ------------------------------
@@ -325,10 +338,11 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
         const int a_per = p.a_stages / p.ng;
         int sa = 0, sa_other = 0, sb = 0, g = 0;
         uint32_t pa = 0, pa_other = 0, pb = 0, it = 0;
-        TileWalker tw(blockIdx.x, gridDim.x, n_tiles, m_tiles);
-        for (uint32_t tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it, tw.next()) {
+        TileWalker tw(cta_first, cta_step, n_tiles, m_tiles);
+        const uint32_t b_half = p.b_stage_bytes >> 1;
+        for (uint32_t tile = cta_first; tile < total_tiles; tile += cta_step, ++it, tw.next()) {
             const TileCoord tc = tw.c;
-            const int nt = tc.nt, mt = tc.mt, b = tc.b;
+            const int nt = tc.nt, mt = tc.mt * mt_mul + static_cast<int>(crank), b = tc.b;
             const int slot0 = g * a_per;
             const int phase = nt / p.tiles_per_phase;
             const int n0 = phase * p.cout_phase + (nt % p.tiles_per_phase) * p.n_tile;
@@ -351,8 +365,13 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                         mbar_wait_warp(&b_empty[sb], pb ^ 1);
                         if (elect_one()) {
                             mbar_arrive_expect_tx(&b_full[sb], p.b_stage_bytes);
-                            tma_load_3d_hint(sB + sb * p.b_stage_bytes, &map_w, &b_full[sb], kb * UMMA_BLOCK_K, n0, j,
-                                             kPolicyEvictLast);
+                            if (p.cluster)  // this CTA fetches its half of the stage and multicasts it to both
+                                tma_load_3d_mc_hint(sB + sb * p.b_stage_bytes + crank * b_half, &map_w, &b_full[sb],
+                                                    kb * UMMA_BLOCK_K, n0 + static_cast<int>(crank) * (p.n_tile >> 1), j, 3,
+                                                    kPolicyEvictLast);
+                            else
+                                tma_load_3d_hint(sB + sb * p.b_stage_bytes, &map_w, &b_full[sb], kb * UMMA_BLOCK_K, n0, j,
+                                                 kPolicyEvictLast);
                         }
                         if (++sb == p.b_stages) { sb = 0; pb ^= 1; }
                     }
@@ -370,10 +389,10 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
         const uint32_t sA_d = smem_u32(sA) >> 4, sB_d = smem_u32(sB) >> 4;
         if (p.stationary)
             umma_issue_loop<true>(p, tmem_base, sA_d, sB_d, a_full, a_empty, b_full, b_empty, acc_full, acc_empty, k_blocks,
-                                  n_tiles, group);
+                                  n_tiles, group, cta_first, cta_step);
         else
             umma_issue_loop<false>(p, tmem_base, sA_d, sB_d, a_full, a_empty, b_full, b_empty, acc_full, acc_empty,
-                                   k_blocks, n_tiles, group);
+                                   k_blocks, n_tiles, group, cta_first, cta_step);
     } else if (warp == 6) {
         // ------------------------------ residual / accum chunk loader ------------------------------
         if (n_ld > 0) {
@@ -383,10 +402,10 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
             const int ld_per = p.ld_stages / p.ng;
             int s = 0, s_other = 0, g = 0;
             uint32_t ps = 0, ps_other = 0;
-            TileWalker tw(blockIdx.x, gridDim.x, n_tiles, m_tiles);
-            for (uint32_t tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, tw.next()) {
+            TileWalker tw(cta_first, cta_step, n_tiles, m_tiles);
+            for (uint32_t tile = cta_first; tile < total_tiles; tile += cta_step, tw.next()) {
                 const TileCoord tc = tw.c;
-                const int nt = tc.nt, t00 = tc.mt * UMMA_BLOCK_M * p.mp, b = tc.b;
+                const int nt = tc.nt, t00 = (tc.mt * mt_mul + static_cast<int>(crank)) * UMMA_BLOCK_M * p.mp, b = tc.b;
                 const int phase = nt / p.tiles_per_phase;
                 const int c0 = (nt % p.tiles_per_phase) * p.n_tile;
                 const int slot0 = g * ld_per;
@@ -433,10 +452,10 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
         uint32_t pacc = 0, pls = 0;
         const bool tracer = (q == 0 && lane == 0);
         uint32_t it = 0;
-        TileWalker tw(blockIdx.x + group * gridDim.x, p.ng * gridDim.x, n_tiles, m_tiles);
-        for (uint32_t tile = blockIdx.x + group * gridDim.x; tile < total_tiles; tile += p.ng * gridDim.x, ++it, tw.next()) {
+        TileWalker tw(cta_first + group * cta_step, p.ng * cta_step, n_tiles, m_tiles);
+        for (uint32_t tile = cta_first + group * cta_step; tile < total_tiles; tile += p.ng * cta_step, ++it, tw.next()) {
             const TileCoord tc = tw.c;
-            const int nt = tc.nt, t00 = tc.mt * UMMA_BLOCK_M * p.mp, b = tc.b;
+            const int nt = tc.nt, t00 = (tc.mt * mt_mul + static_cast<int>(crank)) * UMMA_BLOCK_M * p.mp, b = tc.b;
             const int phase = nt / p.tiles_per_phase;
             const int c0 = (nt % p.tiles_per_phase) * p.n_tile;  // channel offset inside the phase
 
@@ -577,6 +596,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns));
         p.trace[14 * static_cast<size_t>(p.trace_n) + blockIdx.x] = ns;  // CTA end (ns)
     }
+    if (p.cluster) cluster_sync_all();  // the peer's last multicast commits land in this CTA's barriers before it exits
     if (warp == 1) {
         tc_fence_after_sync();
         tmem_dealloc(tmem_base, p.tmem_cols);
@@ -783,13 +803,28 @@ int conv_umma_launch(const void* x, const void* w_packed, const float* bias, con
                                 p.ld_stages * n_ld * EPI_LD_TILE_BYTES + st_bytes + p.bias_smem + 1024 + 1024;
     BVG_REQUIRE(smem_bytes <= 227 * 1024, BVG_ERR_UNSUPPORTED, "conv_umma: %u bytes of shared memory needed", smem_bytes);
 
+    // Cluster mode for SMALL-M weight-streaming layers (one utterance at stages 0-1: 14-54 row tiles of C = 768 / 384).
+    // Every row tile streams the whole weight slice of its N tile from L2; with ~112 CTAs doing that at once the layer is
+    // bound by aggregate L2 bandwidth (99 cycles per MMA against the 56-66-cycle issue floor, tools/conv_first_tile.py).
+    // Two CTAs that work on neighbouring row tiles of the same N tile form a cluster: each fetches half of every weight
+    // stage and multicasts it into both shared memories, halving the L2 reads at an unchanged CTA count.
+    // BVG_CONV_CLUSTER=1 switches it on.
+    static const int cluster_env = []() { const char* e = getenv("BVG_CONV_CLUSTER"); return e ? atoi(e) : 0; }();
+    p.cluster = 0;
+    if (cluster_env && !p.stationary && p.ng == 1 && p.mp == 1 && num_phases == 1 && p.n_tile % 16 == 0 && Cin >= 256 &&
+        p.m_tiles >= 2 && p.total_tiles <= 2 * (int64_t)device_sm_count()) {
+        p.cluster = 1;
+        p.m_tiles = ceil_div(p.m_tiles, 2);  // the kernel walks row-tile PAIRS
+        p.total_tiles = p.m_tiles * B * p.num_phases * p.tiles_per_phase;
+    }
+
     CUtensorMap map_x, map_w, map_res, map_acc, map_y32, map_y16;
     // the A box is a_stage_bytes/128 rows so that expect_tx matches the bytes TMA writes
     const uint32_t a_box_rows = p.a_box_bytes / 128;
     BVG_REQUIRE(a_box_rows <= 256, BVG_ERR_UNSUPPORTED, "conv_umma: halo tile of %u rows exceeds the TMA box limit", a_box_rows);
     int rc = encode_3d_bf16(&map_x, x, (uint64_t)Cin, (uint64_t)T, (uint64_t)B, UMMA_BLOCK_K, a_box_rows, 1, "x");
     if (rc != BVG_OK) return rc;
-    const uint32_t b_box_rows = p.b_stage_bytes / 128;
+    const uint32_t b_box_rows = p.b_stage_bytes / 128 / (p.cluster ? 2 : 1);  // cluster mode: each CTA fetches half a stage
     rc = encode_3d_bf16(&map_w, w_packed, (uint64_t)Cin, (uint64_t)N, (uint64_t)taps, UMMA_BLOCK_K, b_box_rows, 1, "w");
     if (rc != BVG_OK) return rc;
 
@@ -805,7 +840,8 @@ int conv_umma_launch(const void* x, const void* w_packed, const float* bias, con
         }
     }
     const int sms = device_sm_count();
-    const int grid = (int)(p.total_tiles < sms ? p.total_tiles : sms);
+    const int grid = p.cluster ? 2 * (int)(p.total_tiles < sms / 2 ? p.total_tiles : sms / 2)
+                               : (int)(p.total_tiles < sms ? p.total_tiles : sms);
     map_res = map_acc = map_y32 = map_y16 = map_x;  // placeholders for unused maps
     if (p.has_res && (rc = encode_io_4d(&map_res, residual, false, cout_phase, num_phases, T, B, 128, "residual")) != BVG_OK) return rc;
     if (p.has_acc && (rc = encode_io_4d(&map_acc, accum, false, cout_phase, num_phases, T, B, 128, "accum")) != BVG_OK) return rc;
@@ -817,11 +853,22 @@ int conv_umma_launch(const void* x, const void* w_packed, const float* bias, con
         cfg.blockDim = dim3(p.ng == 2 ? UMMA_THREADS2 : UMMA_THREADS);
         cfg.dynamicSmemBytes = smem_bytes;
         cfg.stream = st;
-        cudaLaunchAttribute attr[1];
-        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cudaLaunchAttribute attr[2];
+        int na = 0;
+        if (pdl_enabled()) {
+            attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+            attr[na].val.programmaticStreamSerializationAllowed = 1;
+            ++na;
+        }
+        if (p.cluster) {
+            attr[na].id = cudaLaunchAttributeClusterDimension;
+            attr[na].val.clusterDim.x = 2;
+            attr[na].val.clusterDim.y = 1;
+            attr[na].val.clusterDim.z = 1;
+            ++na;
+        }
         cfg.attrs = attr;
-        cfg.numAttrs = pdl_enabled() ? 1 : 0;
+        cfg.numAttrs = na;
         BVG_CUDA(cudaLaunchKernelEx(&cfg, conv_umma_kernel, map_x, map_w, map_res, map_acc, map_y32, map_y16, p));
     }
     BVG_LAUNCH_CHECK("conv_umma_kernel");

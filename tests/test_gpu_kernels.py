@@ -345,3 +345,17 @@ def test_activation1d_fast_path_far_outside_init_range(ops):
     for precise in (False, True):
         y = ops.activation1d(_t(x), _t(al), _t(be), precise).cpu().numpy()
         assert snr_db(ref, y) > 110.0, (precise, snr_db(ref, y))
+
+
+def test_conv1d_cluster_multicast_mode_subprocess():
+    """BVG_CONV_CLUSTER=1 (clusters of two CTAs share every streamed weight stage by TMA multicast; small-M wide layers
+    only, off by default, read once per process): same results as the default path on even / odd row-tile counts, dilation,
+    residual (tools/conv_cluster_check.py compares with an fp32 conv of the bf16-rounded operands and checks repeatability)."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, BVG_CONV_CLUSTER="1")
+    out = subprocess.run([sys.executable, os.path.join(root, "tools", "conv_cluster_check.py")], capture_output=True, text=True,
+                         timeout=300, env=env)
+    assert out.returncode == 0 and "ALL OK" in out.stdout and "cluster=1" in out.stdout, out.stdout[-1500:] + out.stderr[-1500:]
