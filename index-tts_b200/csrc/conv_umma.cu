@@ -811,8 +811,9 @@ int conv_umma_launch(const void* x, const void* w_packed, const float* bias, con
     // BVG_CONV_CLUSTER=1 switches it on.
     static const int cluster_env = []() { const char* e = getenv("BVG_CONV_CLUSTER"); return e ? atoi(e) : 0; }();
     p.cluster = 0;
-    if (cluster_env && !p.stationary && p.ng == 1 && p.mp == 1 && num_phases == 1 && p.n_tile % 16 == 0 && Cin >= 256 &&
-        p.m_tiles >= 2 && p.total_tiles <= 2 * (int64_t)device_sm_count()) {
+    // BVG_CONV_CLUSTER=2: every weight-streaming single-pipeline layer, whatever its size (experiment)
+    if (cluster_env && !p.stationary && p.ng == 1 && p.mp == 1 && num_phases == 1 && p.n_tile % 16 == 0 && p.m_tiles >= 2 &&
+        (cluster_env >= 2 || (Cin >= 256 && p.total_tiles <= 2 * (int64_t)device_sm_count()))) {
         p.cluster = 1;
         p.m_tiles = ceil_div(p.m_tiles, 2);  // the kernel walks row-tile PAIRS
         p.total_tiles = p.m_tiles * B * p.num_phases * p.tiles_per_phase;
