@@ -302,7 +302,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
     tc_fence_before_sync();
     __syncthreads();
     tc_fence_after_sync();
-    if (p.cluster) cluster_sync_all();  // the peer's barriers exist before any multicast / remote arrive targets them
+    if (p.cluster) cluster_barrier_sync();  // the peer's barriers exist before any multicast / remote arrive targets them
     const uint32_t tmem_base = *tmem_ptr;
 
     const int k_blocks = (p.Cin + UMMA_BLOCK_K - 1) / UMMA_BLOCK_K;
@@ -596,7 +596,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns));
         p.trace[14 * static_cast<size_t>(p.trace_n) + blockIdx.x] = ns;  // CTA end (ns)
     }
-    if (p.cluster) cluster_sync_all();  // the peer's last multicast commits land in this CTA's barriers before it exits
+    if (p.cluster) cluster_barrier_sync();  // the peer's last multicast commits land in this CTA's barriers before it exits
     if (warp == 1) {
         tc_fence_after_sync();
         tmem_dealloc(tmem_base, p.tmem_cols);

@@ -117,7 +117,7 @@ __device__ __forceinline__ void tma_load_3d_mc_hint(void* smem_dst, const CUtens
         ::"r"(smem_u32(smem_dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "h"(cta_mask), "l"(policy)
         : "memory");
 }
-__device__ __forceinline__ void cluster_sync_all() {
+__device__ __forceinline__ void cluster_barrier_sync() {
     asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
 __device__ __forceinline__ void tma_load_4d(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1,
