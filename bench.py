@@ -12,9 +12,12 @@ Printed JSON line (rank 0):
   e2e        same metric through the public module call with HOST mels: pinned H2D copy + forward + D2H of the wav
   roofline   the dominant kernel (tcgen05 implicit-GEMM conv): algorithmic FLOPs of its launches / their CUDA-event
              time, against the measured bf16 peak in MEASURED_PEAKS.json
-  cpu_baseline  the CPU oracle port (oracle/torch_port.py: the reference's op sequence on torch CPU kernels) timed on this box's host cores on a bounded sample
---impl reference: the CPU arm only (the reference is Python/torch and cannot travel to the box; its restatement in
-oracle/ is timed with all host threads), same metric/config/unit.
+  cpu_baseline  the UNMODIFIED reference BigVGAN.forward (baseline/_ref, installed by baseline/install_ref.sh; torch CPU
+             kernels, all host threads) on a bounded sample: two of the batch's 16 utterances.  Falls back to the oracle
+             port (oracle/torch_port.py, kind "port") when baseline/_ref is absent
+  parity     SNR / max-abs of the TIMED output tensor against those two reference runs (same weights)
+--impl reference: the CPU arm only, K timed steps after W warm-up steps, one 10 s utterance of the batch per step
+(utterances are independent, so audio-s/s of the sample is the metric of the workload); same metric/config/unit.
 """
 import argparse
 import json
@@ -104,14 +107,14 @@ def make_state_dict_torch(seed=1234):
 
 
 def cpu_port_audio_s_per_s(steps=1, warmup=1, frames=None, threads=None):
-    """The reference's CPU path restated op for op on torch CPU kernels (oracle/torch_port.py), all host threads,
-    on a bounded sample of the workload: one utterance of `frames` mel frames per step."""
+    """Fallback CPU arm: the reference's CPU path restated op for op on torch CPU kernels (oracle/torch_port.py), all host
+    threads, on a bounded sample of the workload: one utterance of `frames` mel frames per step."""
     import numpy as np
     import torch
     from oracle import bigvgan_oracle as O, torch_port as TP
     threads = threads or os.cpu_count()
     torch.set_num_threads(threads)
-    frames = frames or 431  # 5 s (BASELINE.json configs[0]): 1/32 of the cfg2 batch
+    frames = frames or CFG2_T
     sd = TP.prepare(O.make_state_dict(O.DEFAULT_HPARAMS, seed=1))
     mel = torch.from_numpy(np.random.default_rng(0).standard_normal((1, NUM_MELS, frames)).astype(np.float32))
     for _ in range(warmup):
@@ -121,8 +124,56 @@ def cpu_port_audio_s_per_s(steps=1, warmup=1, frames=None, threads=None):
         TP.forward(sd, mel)
     dt = (time.perf_counter() - t0) / steps
     audio_s = frames * HOP / SR
-    return audio_s / dt, dt, threads, (f"1 utterance x {frames} frames ({audio_s:.2f} s audio) per step, fp32, torch CPU "
-                                       f"kernels, {threads} threads")
+    return audio_s / dt, dt, threads, (f"1 of the batch's 16 utterances ({frames} frames, {audio_s:.2f} s audio) per step, fp32, "
+                                       f"oracle/torch_port.py on torch CPU kernels, {threads} threads"), "port"
+
+
+def reference_cpu_model(state_dict=None):
+    """The UNMODIFIED reference module (baseline/_ref, installed by baseline/install_ref.sh) on the CPU with the bench
+    weights; None when baseline/_ref is absent."""
+    import contextlib
+    import torch
+    from baseline import ref_loader
+    if not ref_loader.available():
+        return None
+    with contextlib.redirect_stdout(sys.stderr):
+        bigvgan, _, _ = ref_loader.import_reference()
+        h = bigvgan.load_hparams_from_json(os.path.join(ROOT, "index-tts_b200", "config.json"))
+        torch.manual_seed(1234)
+        m = bigvgan.BigVGAN(h, use_cuda_kernel=False)
+        m.remove_weight_norm()
+        if state_dict is not None:
+            m.load_state_dict(state_dict, strict=True)
+    return m.eval()
+
+
+def cpu_reference_audio_s_per_s(steps=1, warmup=1, frames=None, threads=None, model=None, mels=None):
+    """CPU arm: the reference's own BigVGAN.forward (bigvgan.py:360-386, torch path, fp32) on the box's host cores, on a
+    bounded sample of the workload -- ONE of the batch's 16 independent utterances per step (same length, same weights).
+    Returns (audio-s/s, s/step, threads, sample text, kind, outputs)."""
+    import torch
+    threads = threads or os.cpu_count()
+    torch.set_num_threads(threads)
+    frames = frames or CFG2_T
+    if model is None:
+        model = reference_cpu_model()
+    if model is None:
+        return cpu_port_audio_s_per_s(steps, warmup, frames, threads) + (None,)
+    if mels is None:
+        g = torch.Generator().manual_seed(1)
+        mels = [torch.randn(1, NUM_MELS, frames, generator=g) for _ in range(max(steps, 1))]
+    outs = []
+    with torch.inference_mode():
+        for i in range(warmup):
+            model(mels[i % len(mels)])
+        t0 = time.perf_counter()
+        for i in range(steps):
+            outs.append(model(mels[i % len(mels)]))
+        dt = (time.perf_counter() - t0) / steps
+    audio_s = frames * HOP / SR
+    sample = (f"1 of the batch's 16 utterances ({frames} frames, {audio_s:.2f} s audio) per step, fp32, the unmodified "
+              f"reference BigVGAN.forward (baseline/_ref) on torch CPU kernels, {threads} threads")
+    return audio_s / dt, dt, threads, sample, "reference", outs
 
 
 _REAL_STDOUT = None
@@ -138,13 +189,34 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
-    v, dt, threads, sample = cpu_port_audio_s_per_s(steps=max(1, min(args.steps, 5)), warmup=min(args.warmup, 1))
+    # every step really runs: K timed steps after W warm-up steps.  A step is one utterance of the cfg2 batch (862 frames,
+    # 10 s); on a slow host the utterance is shortened (431 / 216 / 108 frames -- the sample text says which) so that the
+    # whole K + W run stays within ~3 minutes, calibrated by one untimed 108-frame forward.
+    W = max(0, args.warmup)
+    K = max(1, args.steps)
+    import torch
+    torch.set_num_threads(os.cpu_count())
+    model = reference_cpu_model()
+    frames = CFG2_T
+    if model is not None:
+        with torch.inference_mode():
+            probe = torch.randn(1, NUM_MELS, 108)
+            model(probe)
+            t0 = time.perf_counter()
+            model(probe)
+            per_frame = (time.perf_counter() - t0) / 108
+        budget_s = float(os.environ.get("BVG_REF_BUDGET_S", "180"))
+        while frames > 108 and per_frame * frames * (K + W) > budget_s:
+            frames = (frames + 1) // 2
+    v, dt, threads, sample, kind, _ = cpu_reference_audio_s_per_s(steps=K, warmup=W, frames=frames, model=model)
     line = {
         "impl": "reference", "metric": "vocoder audio-sec/sec (RTF^-1)", "value": v, "unit": "audio-s/s", "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": min(args.warmup, 1), "ms_per_step": dt * 1e3, "higher_is_better": True,
+        "steps": max(1, args.steps), "warmup": W, "ms_per_step": dt * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "note": "CPU arm: bounded sample of the workload"},
-        "cpu_baseline": {"value": v, "unit": "audio-s/s", "cores": threads, "kind": "port", "sample": sample},
+        "config": {"workload": WORKLOAD, "note": "CPU arm: each step is a bounded sample of the workload (one of the 16 "
+                   "independent utterances of the batch); audio-s/s is per-utterance work / time, so it is the same metric",
+                   "runs_on": "rank 0 only, host cores; the other ranks exit"},
+        "cpu_baseline": {"value": v, "unit": "audio-s/s", "cores": threads, "kind": kind, "sample": sample},
         "e2e": {"value": v, "unit": "audio-s/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     emit(line)
@@ -252,15 +324,33 @@ def main():
     mel_long = torch.randn(1, NUM_MELS, long_T, generator=torch.Generator().manual_seed(2)).to(dev)
     fwd = lambda m: model(m)
 
+    long_tm = {}
+
     def step_long():
         with torch.no_grad():
-            return sharding.forward_time_sharded(fwd, mel_long, HOP, dst=0)
+            return sharding.forward_time_sharded(fwd, mel_long, HOP, dst=0, timings=long_tm)
 
     for _ in range(2):
         step_long()
     ms_long = timed(step_long, 3)
+    # compute / stitch split of one more (untimed-as-a-whole) step, per rank, max over ranks
+    barrier()
+    wav_long = step_long()
+    torch.cuda.synchronize()
+    split = torch.tensor([long_tm["t0"].elapsed_time(long_tm["t1"]), long_tm["t1"].elapsed_time(long_tm["t2"])], device=dev)
+    if world > 1:
+        dist.all_reduce(split, op=dist.ReduceOp.MAX)
+    # parity of the stitch: rank 0 also runs the UNSHARDED forward of the same mel once (untimed) and compares
+    long_err = None
+    if rank == 0:
+        with torch.no_grad():
+            ref_long = model(mel_long)
+        long_err = float((wav_long - ref_long).abs().max().item())
+        del ref_long
     long_form = {"workload": "cfg4: one 120 s mel (80x10336) time-sharded over the ranks, 38-frame halo, P2P stitch to rank 0",
                  "value": (long_T * HOP / SR) / (ms_long * 1e-3), "unit": "audio-s/s", "ms": ms_long, "n_gpus": world,
+                 "compute_ms": float(split[0].item()), "stitch_ms": float(split[1].item()),
+                 "max_abs_vs_unsharded": long_err,
                  "redundant_frames_per_rank": 0 if world == 1 else 2 * sharding.RECEPTIVE_HALO_FRAMES,
                  "exchange": "none" if world == 1 else "NCCL send/recv of core waveform pieces (no collective)"}
 
@@ -288,16 +378,25 @@ def main():
     mma_ms = conv["ms"] + convt["ms"]
     mma_flops = conv["flops"] + convt["flops"]
     ach = mma_flops / (mma_ms * 1e-3) / 1e12 if mma_ms > 0 else 0.0
-    traffic = None
+    # DRAM traffic of the dominant kernel from ncu (profiles/ncu_traffic.json, written by tools/ncu_summary.py):
+    # `traffic` is the per-launch AVERAGE of dram__bytes_read.sum + dram__bytes_write.sum over every conv_umma_kernel
+    # launch of one step (same aggregation as `achieved`), when a launch-list capture with those metrics exists;
+    # `traffic_one_launch` is the figure of the single --set full capture (one stage-1 k = 11 layer).
+    traffic, traffic_one = None, None
     tpath = os.path.join(ROOT, "profiles", "ncu_traffic.json")
     if os.path.exists(tpath):
         try:
-            traffic = json.load(open(tpath)).get("conv_umma_kernel_bytes_per_launch")
+            tj = json.load(open(tpath))
+            traffic = tj.get("conv_umma_kernel_bytes_per_launch_avg")
+            traffic_one = {"bytes": tj.get("conv_umma_kernel_bytes_per_launch"), "layer": tj.get("layer"),
+                           "algorithmic_bytes": tj.get("algorithmic_bytes")}
         except Exception:
             traffic = None
     roofline = {"bound": "tensor", "kernel": "conv_umma_kernel (tcgen05 implicit-GEMM conv + polyphase convT)",
                 "achieved": ach, "peak": peaks["tf_sus"], "unit": "TFLOP/s", "frac": ach / peaks["tf_sus"],
-                "traffic": traffic, "launches": conv["n"] + convt["n"], "share_of_step": mma_ms / max(sum(d["ms"] for d in by.values()), 1e-9),
+                "traffic": traffic, "traffic_one_launch": traffic_one,
+                "algorithmic_bytes_per_launch_avg": (conv["bytes"] + convt["bytes"]) / max(conv["n"] + convt["n"], 1),
+                "launches": conv["n"] + convt["n"], "share_of_step": mma_ms / max(sum(d["ms"] for d in by.values()), 1e-9),
                 "peak_source": peaks["source"] + ", sustained bf16 (kernel timed inside a long step)"}
     act = by.get("activation1d")
     kernels = {k: {"ms": round(d["ms"], 4), "launches": d["n"], "roofline_ms": round(d["roof_ms"], 4),
@@ -372,10 +471,33 @@ def main():
         latency = {"workload": "cfg1 shape: 1 x 5 s mel (80x431), " + args.precision, "eager_ms": ms_eager,
                    "cuda_graph_ms": ms_graph, "audio_s_per_s_graph": (431 * HOP / SR) / (ms_graph * 1e-3)}
 
-    cpu = None
+    # ---- CPU baseline + parity of the TIMED tensor: the reference's own forward (fp32, host cores, same weights) on two
+    # of the 16 utterances of the timed batch; the same two runs are the timed CPU baseline (bounded sample).
+    cpu, parity = None, None
     if not args.no_cpu_baseline:
-        v, dt, threads, sample = cpu_port_audio_s_per_s(steps=3, warmup=1)
-        cpu = {"value": v, "unit": "audio-s/s", "cores": threads, "kind": "port", "sample": sample}
+        import numpy as np
+        with contextlib.redirect_stdout(sys.stderr):
+            sd_cpu = {k: v.detach().float().cpu() for k, v in model.state_dict().items()}
+            ref_m = reference_cpu_model(sd_cpu)
+        picks = [0, Bsz - 1] if Bsz > 1 else [0]
+        mels_cpu = [mel_host[i:i + 1].clone() for i in picks]
+        v, dt, threads, sample, kind, outs = cpu_reference_audio_s_per_s(steps=len(picks), warmup=1, frames=T, model=ref_m,
+                                                                         mels=mels_cpu)
+        cpu = {"value": v, "unit": "audio-s/s", "cores": threads, "kind": kind, "sample": sample}
+        if outs is not None:
+            with torch.no_grad():
+                wav_timed = step_resident()  # the tensor the timed loop produces (same inputs, same plan)
+            snrs, errs = [], []
+            for i, o in zip(picks, outs):
+                ours = wav_timed[i].float().cpu().numpy().astype(np.float64).ravel()
+                refw = o[0].numpy().astype(np.float64).ravel()
+                err = ours - refw
+                snrs.append(10.0 * float(np.log10((refw ** 2).sum() / max((err ** 2).sum(), 1e-300))))
+                errs.append(float(np.abs(err).max()))
+            bar = 40.0 if args.precision == "bf16" else 80.0
+            parity = {"against": "the unmodified reference BigVGAN.forward (baseline/_ref), fp32 on CPU, same weights",
+                      "utterances": picks, "snr_db": min(snrs), "snr_db_each": snrs, "max_abs": max(errs),
+                      "bar_snr_db": bar, "ok": bool(min(snrs) >= bar and (args.precision == "bf16" or max(errs) <= 1e-4))}
 
     line = {
         "metric": "vocoder audio-sec/sec (RTF^-1)", "value": world * audio_s / (ms_step * 1e-3), "unit": "audio-s/s",
@@ -397,6 +519,7 @@ def main():
         "v1_generator": v1_line,
         "latency": latency,
         "cpu_baseline": cpu,
+        "parity": parity,
     }
     emit(line)
     if world > 1:

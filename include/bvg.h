@@ -71,6 +71,11 @@ BVG_API int bvg_device_check(int device);
  * gpu_launches claim) */
 BVG_API int64_t bvg_launch_count(void);
 BVG_API void bvg_reset_launch_count(void);
+/* Optional eager initialisation for `device` (< 0: the current device) on the calling host thread: creates the forward
+ * plan's auxiliary streams / events and sets the kernels' shared-memory attributes, all of which are otherwise created on
+ * first use.  A caller whose first bvg_forward would run under a global-mode stream capture (where stream and event
+ * creation is illegal) calls this once before capturing.  No reference counterpart (torch initialises lazily too). */
+BVG_API int bvg_init(int device);
 
 /* ---------------------------------------------------------------------------------------------------------- */
 /* (a) fused anti-aliased activation: y = down2(snake_beta(up2(x)))
@@ -256,10 +261,12 @@ BVG_API int bvg_forward_cond_profile(const bvg_model_desc* m_host, const float* 
                              void* workspace, size_t workspace_bytes, void* stream, bvg_launch_record* records_host,
                              int max_records, int* n_records);
 
-/* Developer instrumentation (no reference counterpart): when `buf` is a device buffer of 16 * n_tiles uint64 the next
- * tcgen05 conv launches record SM cycle counters of CTA 0's pipeline roles (TMA producer / UMMA issuer / epilogue) for
- * their first n_tiles tiles (tools/conv_timeline.py).  Pass NULL to switch it off (the default). */
-BVG_API void bvg_debug_conv_trace(void* buf, int n_tiles);
+/* Developer instrumentation (no reference counterpart), live only in a library built with -DBVG_CONV_TRACE
+ * (tools/build_variant.sh): when `buf` is a device buffer of 16 * n_tiles uint64 the next tcgen05 conv launches record SM
+ * cycle counters of CTA 0's pipeline roles (TMA producer / UMMA issuer / epilogue) for their first n_tiles tiles
+ * (tools/conv_timeline.py).  Pass NULL to switch it off.  The shipped build keeps NO trace state: it returns
+ * BVG_ERR_UNSUPPORTED for a non-NULL buffer. */
+BVG_API int bvg_debug_conv_trace(void* buf, int n_tiles);
 
 #ifdef __cplusplus
 }

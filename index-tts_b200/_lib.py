@@ -66,6 +66,7 @@ SIGNATURES = {
     "bvg_device_check": (c_int, [c_int]),
     "bvg_launch_count": (c_i64, []),
     "bvg_reset_launch_count": (None, []),
+    "bvg_init": (c_int, [c_int]),
     "bvg_activation1d_fwd": (c_int, [c_vp, c_vp, c_vp, c_vp, c_i64, c_i64, c_i64, c_i64, c_i64, c_int, c_int, c_vp]),
     "bvg_activation1d_nlc_fwd": (c_int, [c_vp, c_int, c_vp, c_int, c_vp, c_vp, c_i64, c_i64, c_i64, c_int, c_vp]),
     "bvg_activation1d_nlc_multi_fwd": (c_int, [c_vp, c_int, C.POINTER(c_vp), c_int, C.POINTER(c_vp), C.POINTER(c_vp), c_int,
@@ -88,7 +89,7 @@ SIGNATURES = {
                                     C.POINTER(LaunchRecord), c_int, C.POINTER(c_int)]),
     "bvg_forward_cond_profile": (c_int, [C.POINTER(ModelDesc), c_vp, c_int, c_i64, c_i64, C.POINTER(c_vp), c_vp, c_i64, c_i64,
                                          c_vp, c_sz, c_vp, C.POINTER(LaunchRecord), c_int, C.POINTER(c_int)]),
-    "bvg_debug_conv_trace": (None, [c_vp, c_int]),
+    "bvg_debug_conv_trace": (c_int, [c_vp, c_int]),
     "bvg_cond_linear_fwd": (c_int, [c_vp, c_vp, c_vp, c_vp, c_i64, c_i64, c_i64, c_vp]),
     "bvg_add_channel_vector_nlc": (c_int, [c_vp, c_int, c_vp, c_vp, c_int, c_i64, c_i64, c_i64, c_vp]),
     "bvg_forward_cond": (c_int, [C.POINTER(ModelDesc), c_vp, c_int, c_i64, c_i64, C.POINTER(c_vp), c_vp, c_i64, c_i64,

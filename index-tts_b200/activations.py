@@ -1,8 +1,8 @@
 """Parameter containers for Snake / SnakeBeta (reference ``bigvgan/activations.py:9-120``).
 
-Inside the generator these modules are never *called*: ``Activation1d`` hands their ``alpha`` / ``beta`` to the
-fused sm_100a kernel.  ``forward`` is kept for API parity (elementwise, any device) so code that applies a bare
-``SnakeBeta`` keeps working; it is not on the hot path.
+These modules only *store* ``alpha`` / ``beta``: ``Activation1d`` hands them to the fused sm_100a kernel.  The reference
+never applies a bare ``Snake`` / ``SnakeBeta`` (always through ``Activation1d``: bigvgan.py:94-130, 343-357), and this
+package has no torch compute path, so calling ``forward`` on the bare module raises.
 """
 import torch
 from torch import nn
@@ -24,10 +24,8 @@ class Snake(nn.Module):
         self.no_div_by_zero = 0.000000001
 
     def forward(self, x):
-        alpha = self.alpha.unsqueeze(0).unsqueeze(-1)
-        if self.alpha_logscale:
-            alpha = torch.exp(alpha)
-        return x + (1.0 / (alpha + self.no_div_by_zero)) * torch.sin(x * alpha) ** 2
+        raise NotImplementedError("Snake is a parameter holder here: wrap it in Activation1d (the fused sm_100a kernel); "
+                                  "this package has no torch compute path")
 
 
 class SnakeBeta(nn.Module):
@@ -48,9 +46,5 @@ class SnakeBeta(nn.Module):
         self.no_div_by_zero = 0.000000001
 
     def forward(self, x):
-        alpha = self.alpha.unsqueeze(0).unsqueeze(-1)
-        beta = self.beta.unsqueeze(0).unsqueeze(-1)
-        if self.alpha_logscale:
-            alpha = torch.exp(alpha)
-            beta = torch.exp(beta)
-        return x + (1.0 / (beta + self.no_div_by_zero)) * torch.sin(x * alpha) ** 2
+        raise NotImplementedError("SnakeBeta is a parameter holder here: wrap it in Activation1d (the fused sm_100a "
+                                  "kernel); this package has no torch compute path")

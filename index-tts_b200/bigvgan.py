@@ -571,6 +571,9 @@ class _GeneratorPlanMixin:
         self.__dict__["_bvg_plan"] = None
         self.__dict__["_bvg_plan_key"] = None
         self.__dict__["_bvg_graph_max_frames"] = int(os.environ.get("BVG_GRAPH_MAX_FRAMES", "0") or 0)
+        self.__dict__["_bvg_gen"] = 0
+        self.__dict__["_bvg_plan_fast"] = None
+        self.__dict__["_bvg_plan_calls"] = 0
 
     def set_cuda_graphs(self, max_frames: int):
         """Extra (not in the reference): replay calls with ``B * T_mel <= max_frames`` from CUDA graphs (one graph per
@@ -584,6 +587,7 @@ class _GeneratorPlanMixin:
     def set_precision(self, precision: str):
         ops.precision_code(precision)
         self.__dict__["_bvg_precision"] = precision
+        self._bump_generation()
         for m in self.modules():
             if isinstance(m, (Conv1d, ConvTranspose1d, AMPBlock1, AMPBlock2)):
                 m.bvg_precision = precision
@@ -593,17 +597,61 @@ class _GeneratorPlanMixin:
     def precision(self) -> str:
         return self.__dict__["_bvg_precision"]
 
+    # ---- plan cache invalidation -------------------------------------------------------------------------------------
+    # The packed plan is valid while no parameter changed.  Walking the module tree for (data_ptr, _version) of all
+    # ~450-780 parameters on every forward cost 1.5-2 ms of host time -- as much as the whole single-utterance GPU step --
+    # so the per-call check is reduced to the `_version` counters of a CACHED parameter list (60 us; catches every
+    # in-place edit made through torch ops: `p.mul_()`, `p.copy_()`, optimizer steps), and the full walk happens only when
+    # a generation counter says the parameter SET may have changed: it is bumped by every hook through which torch
+    # replaces parameters or their storage (`_apply`: .to()/.cuda()/.half(); `load_state_dict`; `remove_weight_norm`;
+    # `set_precision`) and by `invalidate_plan()`.  Edits through `p.data` (`p.data.copy_()`, `.data.normal_()` as in
+    # `init_weights`) bump neither counter -- torch offers no hook -- so such callers call `invalidate_plan()`; as a
+    # safety net the full fingerprint (incl. data pointers) is re-taken every PLAN_RECHECK_CALLS forwards.
+    PLAN_RECHECK_CALLS = 64
+
+    def invalidate_plan(self):
+        """Extra (not in the reference): drop the packed-weight plan; the next forward re-folds and re-packs the weights.
+        Needed only after parameter edits that bypass torch's version counters (``p.data.copy_()``,
+        ``init_weights``-style ``.data.normal_()``)."""
+        self._bump_generation()
+        self.__dict__["_bvg_plan"] = None
+        self.__dict__["_bvg_plan_key"] = None
+        return self
+
+    def _bump_generation(self):
+        self.__dict__["_bvg_gen"] = self.__dict__.get("_bvg_gen", 0) + 1
+
+    def _apply(self, fn, *args, **kwargs):
+        self._bump_generation()
+        return super()._apply(fn, *args, **kwargs)
+
+    def load_state_dict(self, *args, **kwargs):
+        self._bump_generation()
+        return super().load_state_dict(*args, **kwargs)
+
     def _plan(self, device: torch.device) -> _PackedGenerator:
-        prec = ops.precision_code(self.__dict__["_bvg_precision"])
-        key = (device, prec, tuple((p.data_ptr(), p._version) for p in self.parameters()))
-        if self.__dict__["_bvg_plan"] is None or self.__dict__["_bvg_plan_key"] != key:
-            for p in self.parameters():
+        d = self.__dict__
+        prec = ops.precision_code(d["_bvg_precision"])
+        plan = d["_bvg_plan"]
+        fast = (device, prec, d.get("_bvg_gen", 0))
+        if plan is not None and d.get("_bvg_plan_fast") == fast:
+            d["_bvg_plan_calls"] = d.get("_bvg_plan_calls", 0) + 1
+            if d["_bvg_plan_calls"] % self.PLAN_RECHECK_CALLS != 0 and \
+                    [p._version for p in d["_bvg_plan_params"]] == d["_bvg_plan_versions"]:
+                return plan
+        params = list(self.parameters())
+        key = (device, prec, tuple((p.data_ptr(), p._version) for p in params))
+        if plan is None or d["_bvg_plan_key"] != key:
+            for p in params:
                 if p.device != device:
                     raise _lib.BvgError(f"generator parameters live on {p.device} but the input is on {device}; "
                                         "call .to(device) first")
-            self.__dict__["_bvg_plan"] = _PackedGenerator(self, device, prec)
-            self.__dict__["_bvg_plan_key"] = key
-        return self.__dict__["_bvg_plan"]
+            d["_bvg_plan"] = _PackedGenerator(self, device, prec)
+            d["_bvg_plan_key"] = key
+        d["_bvg_plan_fast"] = fast
+        d["_bvg_plan_params"] = params
+        d["_bvg_plan_versions"] = [p._version for p in params]
+        return d["_bvg_plan"]
 
 
 class BigVGAN(
@@ -706,6 +754,7 @@ class BigVGAN(
         return _vocoder_forward_pcm16(x, plan.plan_id, plan.hop)
 
     def remove_weight_norm(self):
+        self._bump_generation()
         try:
             print("Removing weight norm...")
             for l in self.ups:

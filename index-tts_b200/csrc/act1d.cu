@@ -21,6 +21,7 @@
 #include "sm100_ptx.cuh"
 #include "tma_host.cuh"
 
+#include <atomic>
 #include <cstdlib>
 
 #ifndef BVG_ACT_SMEM_KB_DEFAULT
@@ -718,6 +719,22 @@ static int launch_nlc(const void* x, void* y, const float* alpha, const float* b
     return BVG_OK;
 }
 
+// Function attributes of one instantiation, set once per device (two driver calls per launch were a measurable part of
+// the host time in front of every single-utterance forward).  Same L1/shared split as the conv kernel, so that CTAs of
+// the two kernels can be resident on one SM at the same time.
+template <typename TIn, typename TOut, int NH>
+static int act_tma_attrs(bool precise) {
+    static std::atomic<bool> done[2][64];
+    int dev = 0;
+    BVG_CUDA(cudaGetDevice(&dev));
+    if (dev >= 0 && dev < 64 && done[precise ? 1 : 0][dev].load(std::memory_order_acquire)) return BVG_OK;
+    auto kern = precise ? act1d_nlc_tma_kernel<TIn, TOut, true, NH> : act1d_nlc_tma_kernel<TIn, TOut, false, NH>;
+    BVG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024));
+    BVG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    if (dev >= 0 && dev < 64) done[precise ? 1 : 0][dev].store(true, std::memory_order_release);
+    return BVG_OK;
+}
+
 // TMA-pipelined launcher.  Returns BVG_OK after launching, or a positive value when the shape does not suit the TMA
 // path (C not a multiple of 8, ...) and the caller should use the direct-load kernel.
 template <typename TIn, typename TOut, int NH>
@@ -801,9 +818,10 @@ static int launch_nlc_tma(const void* x, const ActHeads<NH>& hd, int64_t B, int6
     BVG_REQUIRE(r == CUDA_SUCCESS, BVG_ERR_CUDA, "cuTensorMapEncodeTiled(activation input) failed with CUresult %d", (int)r);
 
     auto kern = precise ? act1d_nlc_tma_kernel<TIn, TOut, true, NH> : act1d_nlc_tma_kernel<TIn, TOut, false, NH>;
-    BVG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024));
-    // same L1/shared split as the conv kernel: CTAs of the two kernels can then be resident on one SM at the same time
-    BVG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    {
+        const int rc_attr = act_tma_attrs<TIn, TOut, NH>(precise != 0);
+        if (rc_attr != BVG_OK) return rc_attr;
+    }
     static const int grid_mode = []() { const char* e = getenv("BVG_ACT_GRID"); return e ? atoi(e) : 0; }();
     const long long max_ctas = (long long)act_tma_min_ctas(NH) * sms;
     int grid = static_cast<int>(units < max_ctas ? units : max_ctas);
@@ -823,6 +841,20 @@ static int launch_nlc_tma(const void* x, const ActHeads<NH>& hd, int64_t B, int6
         BVG_CUDA(cudaLaunchKernelEx(&cfg, kern, map, hd, p));
     }
     BVG_LAUNCH_CHECK("act1d_nlc_tma_kernel");
+    return BVG_OK;
+}
+
+// bvg_init(): attributes of every instantiation the forward plan launches
+int activation1d_init() {
+    for (int precise = 0; precise < 2; ++precise) {
+        int rc = act_tma_attrs<float, __nv_bfloat16, 1>(precise);
+        if (rc == BVG_OK) rc = act_tma_attrs<float, float, 1>(precise);
+        if (rc == BVG_OK) rc = act_tma_attrs<__nv_bfloat16, __nv_bfloat16, 1>(precise);
+        if (rc == BVG_OK) rc = act_tma_attrs<__nv_bfloat16, float, 1>(precise);
+        if (rc == BVG_OK) rc = act_tma_attrs<float, __nv_bfloat16, 3>(precise);
+        if (rc == BVG_OK) rc = act_tma_attrs<float, float, 3>(precise);
+        if (rc != BVG_OK) return rc;
+    }
     return BVG_OK;
 }
 

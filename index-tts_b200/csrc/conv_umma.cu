@@ -26,6 +26,7 @@
 #include "sm100_ptx.cuh"
 #include "tma_host.cuh"
 
+#include <atomic>
 #include <cstdlib>
 
 #ifndef BVG_CONV_SMEM_KB_DEFAULT
@@ -92,10 +93,15 @@ struct ConvUmmaParams {
     float out_scale;
 };
 
-// Developer timeline: event e of pipeline role `slot` at the role's i-th tile (CTA 0 only).
+// Developer timeline: event e of pipeline role `slot` at the role's i-th tile (CTA 0 only).  Compiled in only with
+// -DBVG_CONV_TRACE (tools/build_variant.sh): the shipped library carries no trace pointer and no global state for it.
 __device__ __forceinline__ void trace_ev(const ConvUmmaParams& p, int slot, uint32_t i) {
+#ifdef BVG_CONV_TRACE
     if (p.trace != nullptr && blockIdx.x == 0 && i < static_cast<uint32_t>(p.trace_n))
         p.trace[static_cast<size_t>(slot) * p.trace_n + i] = clock64();
+#else
+    (void)p; (void)slot; (void)i;
+#endif
 }
 
 // Tile index -> (n tile, m tile, batch item), 32-bit arithmetic (total_tiles < 2^31 is checked by the launcher).
@@ -274,11 +280,13 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
 
+#ifdef BVG_CONV_TRACE
     if (p.trace != nullptr && threadIdx.x == 0 && gridDim.x <= static_cast<unsigned>(p.trace_n)) {
         unsigned long long ns;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns));
         p.trace[13 * static_cast<size_t>(p.trace_n) + blockIdx.x] = ns;  // CTA start (ns)
     }
+#endif
     // PDL: the next kernel of the stream may become resident as soon as this CTA's resources free up; everything this
     // kernel does before griddep_wait() below (barrier init, TMEM allocation, bias copy, stationary weight loads) only
     // touches constants, so it overlaps the tail of the previous kernel.
@@ -591,11 +599,13 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
 
     tc_fence_before_sync();
     __syncthreads();
+#ifdef BVG_CONV_TRACE
     if (p.trace != nullptr && threadIdx.x == 0 && gridDim.x <= static_cast<unsigned>(p.trace_n)) {
         unsigned long long ns;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns));
         p.trace[14 * static_cast<size_t>(p.trace_n) + blockIdx.x] = ns;  // CTA end (ns)
     }
+#endif
     if (p.cluster) cluster_barrier_sync();  // the peer's last multicast commits land in this CTA's barriers before it exits
     if (warp == 1) {
         tc_fence_after_sync();
@@ -643,8 +653,10 @@ static int encode_io_4d(CUtensorMap* map, const void* ptr, bool bf16, uint64_t c
     return BVG_OK;
 }
 
+#ifdef BVG_CONV_TRACE
 static unsigned long long* g_conv_trace = nullptr;
 static int g_conv_trace_n = 0;
+#endif
 
 // Shared-memory budget of one CTA.  Below the 227 KB maximum an Activation1d CTA of another AMP block can be resident
 // on the same SM (forward.cu runs the blocks on separate streams), trading pipeline depth for FP32/tensor overlap.
@@ -656,6 +668,21 @@ static int64_t conv_smem_budget() {
         return (int64_t)kb * 1024;
     }();
     return v;
+}
+
+// Opt in to the large dynamic shared memory carve-out once per device (idempotent calls; the flag is atomic so that
+// concurrent host threads race benignly: at worst both set the same attributes).  Also reachable through bvg_init().
+int conv_umma_init() {
+    static std::atomic<bool> attr_set[64];
+    int dev = 0;
+    BVG_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64 || !attr_set[dev].load(std::memory_order_acquire)) {
+        BVG_CUDA(cudaFuncSetAttribute(conv_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        BVG_CUDA(cudaFuncSetAttribute(conv_umma_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                      cudaSharedmemCarveoutMaxShared));
+        if (dev >= 0 && dev < 64) attr_set[dev].store(true, std::memory_order_release);
+    }
+    return BVG_OK;
 }
 
 // Generic launcher: plain conv (num_phases = 1) or polyphase transposed conv.
@@ -728,8 +755,10 @@ int conv_umma_launch(const void* x, const void* w_packed, const float* bias, con
     p.a_stage_bytes = p.mp == 2 ? 16384u + p.a_box_bytes : p.a_box_bytes;
     p.b_stage_bytes = (uint32_t)round_up((int64_t)p.n_tile * 128, 1024);
     p.ng = 1;
+#ifdef BVG_CONV_TRACE
     p.trace = g_conv_trace;
     p.trace_n = g_conv_trace_n;
+#endif
     p.has_res = residual != nullptr; p.has_acc = accum != nullptr;
     p.has_y32 = y_f32 != nullptr; p.has_y16 = y_bf16 != nullptr;
     const int n_ld = p.has_res + p.has_acc;
@@ -829,16 +858,9 @@ int conv_umma_launch(const void* x, const void* w_packed, const float* bias, con
     rc = encode_3d_bf16(&map_w, w_packed, (uint64_t)Cin, (uint64_t)N, (uint64_t)taps, UMMA_BLOCK_K, b_box_rows, 1, "w");
     if (rc != BVG_OK) return rc;
 
-    {   // opt in to the large dynamic shared memory carve-out once per device
-        static bool attr_set[64] = {};
-        int dev = 0;
-        BVG_CUDA(cudaGetDevice(&dev));
-        if (dev < 0 || dev >= 64 || !attr_set[dev]) {
-            BVG_CUDA(cudaFuncSetAttribute(conv_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-            BVG_CUDA(cudaFuncSetAttribute(conv_umma_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
-                                          cudaSharedmemCarveoutMaxShared));
-            if (dev >= 0 && dev < 64) attr_set[dev] = true;
-        }
+    {
+        const int rc_init = conv_umma_init();
+        if (rc_init != BVG_OK) return rc_init;
     }
     const int sms = device_sm_count();
     const int grid = p.cluster ? 2 * (int)(p.total_tiles < sms / 2 ? p.total_tiles : sms / 2)
@@ -878,7 +900,16 @@ int conv_umma_launch(const void* x, const void* w_packed, const float* bias, con
 
 }  // namespace bvg
 
-extern "C" void bvg_debug_conv_trace(void* buf, int n_tiles) {
+// Developer timeline switch.  Only a library built with -DBVG_CONV_TRACE keeps the pointer (process-global, developer
+// builds only); the shipped build exports the symbol as a no-op that reports BVG_ERR_UNSUPPORTED.
+extern "C" int bvg_debug_conv_trace(void* buf, int n_tiles) {
+#ifdef BVG_CONV_TRACE
     bvg::g_conv_trace = static_cast<unsigned long long*>(buf);
     bvg::g_conv_trace_n = buf ? n_tiles : 0;
+    return BVG_OK;
+#else
+    (void)n_tiles;
+    if (buf == nullptr) return BVG_OK;
+    return bvg::set_error(BVG_ERR_UNSUPPORTED, "bvg_debug_conv_trace: this libbvg.so was built without -DBVG_CONV_TRACE");
+#endif
 }

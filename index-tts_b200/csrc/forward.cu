@@ -158,22 +158,43 @@ struct AuxStreams {
     bool ok = false;
 };
 
+// One entry per (host thread, device), looked up by the exact device ordinal (a process may drive any number of GPUs).
 static AuxStreams* aux_streams() {
-    static thread_local AuxStreams cache[8];
+    static thread_local std::vector<AuxStreams*> cache;
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess) return nullptr;
-    AuxStreams& a = cache[dev & 7];
-    if (a.ok && a.dev == dev) return &a;
-    if (a.ok) return nullptr;  // slot taken by another device: run serially
-    a.dev = dev;
-    bool good = cudaEventCreateWithFlags(&a.fork, cudaEventDisableTiming) == cudaSuccess;
+    for (AuxStreams* a : cache)
+        if (a->dev == dev) return a->ok ? a : nullptr;
+    AuxStreams* a = new AuxStreams();
+    a->dev = dev;
+    bool good = cudaEventCreateWithFlags(&a->fork, cudaEventDisableTiming) == cudaSuccess;
     for (int i = 0; good && i < BVG_MAX_KERNELS - 1; ++i)
-        good = cudaStreamCreateWithFlags(&a.s[i], cudaStreamNonBlocking) == cudaSuccess;
+        good = cudaStreamCreateWithFlags(&a->s[i], cudaStreamNonBlocking) == cudaSuccess;
     for (int i = 0; good && i < BVG_MAX_KERNELS; ++i)
-        good = cudaEventCreateWithFlags(&a.last[i], cudaEventDisableTiming) == cudaSuccess;
-    a.ok = good;
-    return good ? &a : nullptr;
+        good = cudaEventCreateWithFlags(&a->last[i], cudaEventDisableTiming) == cudaSuccess;
+    a->ok = good;
+    cache.push_back(a);
+    return good ? a : nullptr;
 }
+
+// Joins the auxiliary streams back into the caller's stream on EVERY exit path of a stage: an error return between the
+// fork and the regular join must not leave kernels of the aux streams running behind the caller's back (the caller frees
+// the workspace in stream order on `st`) nor a stream capture with dangling forked streams.
+struct AuxJoin {
+    AuxStreams* aux;
+    cudaStream_t st;
+    int n;          // aux streams forked (num_kernels - 1), 0 = nothing to join
+    AuxJoin(AuxStreams* a, cudaStream_t s) : aux(a), st(s), n(0) {}
+    void forked(int num_kernels) { n = num_kernels - 1; }
+    void joined() { n = 0; }
+    ~AuxJoin() {
+        if (aux == nullptr) return;
+        for (int j = 0; j < n; ++j) {
+            // a fresh record on each aux stream covers whatever was queued there before the error
+            if (cudaEventRecord(aux->last[j + 1], aux->s[j]) == cudaSuccess) cudaStreamWaitEvent(st, aux->last[j + 1], 0);
+        }
+    }
+};
 
 // BVG_ACT_MULTI=0: one Activation1d launch per AMP block at the top of a stage instead of the shared-up-sampler kernel
 static int act_multi_requested() {
@@ -217,6 +238,30 @@ extern "C" int bvg_convtranspose1d_nlc_fwd(const void* x, const void* w_packed, 
                                            int precision, void* stream) {
     return convtranspose1d(precision, x, w_packed, bias, y_f32, y_bf16, B, Tin, Cin, Cout, K, u,
                            static_cast<cudaStream_t>(stream));
+}
+
+namespace bvg {
+int conv_umma_init();
+int activation1d_init();
+}  // namespace bvg
+
+// Pre-creates everything the library would otherwise create lazily inside the first call on this (host thread, device):
+// the auxiliary streams / events of the forward plan and the kernels' shared-memory attributes.  Optional -- every entry
+// point initialises on demand -- but a caller whose FIRST call would happen under a global-mode stream capture (where
+// stream / event creation is illegal) calls this once beforehand.
+extern "C" int bvg_init(int device) {
+    int prev = 0;
+    BVG_CUDA(cudaGetDevice(&prev));
+    if (device < 0) device = prev;
+    int rc = bvg_device_check(device);
+    if (rc != BVG_OK) return rc;
+    if (device != prev) BVG_CUDA(cudaSetDevice(device));
+    rc = conv_umma_init();
+    if (rc == BVG_OK) rc = activation1d_init();
+    if (rc == BVG_OK && aux_streams() == nullptr)
+        rc = set_error(BVG_ERR_CUDA, "bvg_init: could not create the auxiliary streams / events on device %d", device);
+    if (device != prev) cudaSetDevice(prev);
+    return rc;
 }
 
 extern "C" size_t bvg_workspace_bytes(const bvg_model_desc* m, int64_t B, int64_t T_mel) {
@@ -341,9 +386,11 @@ static int forward_impl(const bvg_model_desc* m, const float* mel, int mel_layou
             rc = activation1d_nlc_multi(X, BVG_F32, ys, op_dt, als, bes, m->num_kernels, B, T, C, precise, st);
             if (rc != BVG_OK) return rc;
         }
+        AuxJoin join_guard(aux, st);
         if (aux) {
             BVG_CUDA(cudaEventRecord(aux->fork, st));
             for (int j = 1; j < m->num_kernels; ++j) BVG_CUDA(cudaStreamWaitEvent(aux->s[j - 1], aux->fork, 0));
+            join_guard.forked(m->num_kernels);
         }
         for (int j = 0; j < m->num_kernels; ++j) {
             cudaStream_t sj = (aux && j > 0) ? aux->s[j - 1] : st;
@@ -400,7 +447,10 @@ static int forward_impl(const bvg_model_desc* m, const float* mel, int mel_layou
                 if (rc != BVG_OK) return rc;
             }
         }
-        if (aux) BVG_CUDA(cudaStreamWaitEvent(st, aux->last[m->num_kernels - 1], 0));  // join
+        if (aux) {  // join: the last block's final conv waited for every other block's (event chain)
+            BVG_CUDA(cudaStreamWaitEvent(st, aux->last[m->num_kernels - 1], 0));
+            join_guard.joined();
+        }
         stage_in = tc ? SUMOP : static_cast<const void*>(SUM);
     }
     // activation_post -> conv_post -> clamp / tanh (bigvgan.py:378-384), fp32 in both modes

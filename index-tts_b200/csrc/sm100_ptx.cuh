@@ -57,17 +57,30 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
         : "memory");
     return ok != 0;
 }
-// Bounded wait: a protocol bug must not hang the GPU (the box is shared); it traps instead, which the host
-// sees as a launch failure.  ~4 s at 2 GHz.
+// Waits.  Every wait is bounded by a watchdog so that a pipeline-protocol bug traps (the host sees a launch failure)
+// instead of hanging a shared GPU -- but the budget is ~60 s of SM clocks, not a few seconds: under PDL a successor CTA
+// legitimately spins on its barriers while its producer warp sits in griddepcontrol.wait behind its predecessor, and ncu
+// replay, compute-sanitizer, cuda-gdb or a time-sliced GPU stretch every wait without any protocol bug.  After a short
+// busy phase the spin backs off with nanosleep (frees issue slots for the warps being waited for).  -DBVG_NO_MBAR_WATCHDOG
+// removes the bound altogether ("watchdog").
 #ifndef BVG_MBAR_TIMEOUT_CYCLES
-#define BVG_MBAR_TIMEOUT_CYCLES (8000000000ll)
+#define BVG_MBAR_TIMEOUT_CYCLES (120000000000ll)
 #endif
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-    if (mbar_try_wait(bar, parity)) return;
-    const long long t0 = clock64();
-    while (!mbar_try_wait(bar, parity)) {
-        if (clock64() - t0 > BVG_MBAR_TIMEOUT_CYCLES) __trap();
+__device__ __forceinline__ void mbar_backoff(uint32_t& spins, long long& t0) {
+    if (++spins < 2048u) return;
+    __nanosleep(64);
+#ifndef BVG_NO_MBAR_WATCHDOG
+    if ((spins & 1023u) == 0u) {
+        const long long now = clock64();
+        if (t0 == 0) t0 = now;
+        else if (now - t0 > BVG_MBAR_TIMEOUT_CYCLES) __trap();
     }
+#endif
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t spins = 0;
+    long long t0 = 0;
+    while (!mbar_try_wait(bar, parity)) mbar_backoff(spins, t0);
 }
 
 // Wait executed by a full, converged warp.  The loop condition is a warp vote, so the branch is warp-uniform BY
@@ -75,9 +88,8 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 // descriptors) in uniform registers instead of moving them there with R2UR before every tcgen05.mma / TMA issue.
 __device__ __forceinline__ void mbar_wait_warp(uint64_t* bar, uint32_t parity) {
     uint32_t spins = 0;
-    while (!__all_sync(0xffffffffu, mbar_try_wait(bar, parity))) {
-        if (++spins > 400000000u) __trap();  // protocol bug: trap instead of hanging the (shared) GPU
-    }
+    long long t0 = 0;
+    while (!__all_sync(0xffffffffu, mbar_try_wait(bar, parity))) mbar_backoff(spins, t0);
 }
 
 // ------------------------------------------------------------------------------------------------

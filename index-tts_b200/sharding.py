@@ -79,13 +79,18 @@ def run_time_shard(forward_fn: Callable[[torch.Tensor], torch.Tensor], mel: torc
 def forward_time_sharded(forward_fn: Callable[[torch.Tensor], torch.Tensor], mel: Optional[torch.Tensor], hop: int,
                          n_frames: Optional[int] = None, dst: int = 0, group=None,
                          halo: int = RECEPTIVE_HALO_FRAMES, mel_on_all_ranks: bool = True,
-                         num_mels: int = 80, batch: int = 1, device=None) -> Optional[torch.Tensor]:
+                         num_mels: int = 80, batch: int = 1, device=None,
+                         timings: Optional[dict] = None) -> Optional[torch.Tensor]:
     """Vocode one long mel across the ranks of ``group``; the stitched waveform is returned on rank ``dst`` (None
     elsewhere).
 
     ``mel_on_all_ranks=True``: every rank already holds the full mel (it is tiny -- 3.3 MB for 120 s) and slices its
     own range.  ``False``: only ``dst`` holds it and P2P-sends each rank its padded range first (``n_frames``,
     ``num_mels``, ``batch`` and ``device`` must then be given on the other ranks).
+
+    ``timings`` (measurement only, CUDA tensors): a dict that receives the CUDA events ``t0`` (start), ``t1`` (this
+    rank's forward queued) and ``t2`` (stitch done) recorded on the current stream, so that a caller can split the
+    step into compute and stitch time per rank (bench.py ``long_form.compute_ms`` / ``stitch_ms``).
     """
     rank, world = _rank_world(group)
     if mel is not None:
@@ -96,8 +101,18 @@ def forward_time_sharded(forward_fn: Callable[[torch.Tensor], torch.Tensor], mel
     shards = time_shards(n_frames, world, halo)
     mine = shards[rank]
 
+    def mark(name):
+        if timings is not None and torch.cuda.is_available():
+            ev = torch.cuda.Event(enable_timing=True)
+            ev.record()
+            timings[name] = ev
+
+    mark("t0")
     if world == 1:
-        return run_time_shard(forward_fn, mel, mine, hop)
+        out1 = run_time_shard(forward_fn, mel, mine, hop)
+        mark("t1")
+        mark("t2")
+        return out1
 
     # ---- scatter (only when the mel lives on dst alone): P2P sends of the padded ranges --------------------
     if not mel_on_all_ranks:
@@ -117,6 +132,7 @@ def forward_time_sharded(forward_fn: Callable[[torch.Tensor], torch.Tensor], mel
                                                             mine.hi - mine.lo), hop)
     else:
         piece = run_time_shard(forward_fn, mel, mine, hop)
+    mark("t1")
 
     # ---- stitch: every rank's core piece goes straight into its slice of dst's output ----------------------
     if rank == dst:
@@ -138,9 +154,11 @@ def forward_time_sharded(forward_fn: Callable[[torch.Tensor], torch.Tensor], mel
             q.wait()
         for sl, buf in stage:
             sl.copy_(buf)
+        mark("t2")
         return out
     if mine.core_hi > mine.core_lo:
         dist.send(piece.contiguous(), _global_rank(group, dst), group=group)
+    mark("t2")
     return None
 
 

@@ -163,6 +163,7 @@ class BigVGAN(_GeneratorPlanMixin, torch.nn.Module):
         return self.forward_with_embedding(x, speaker_embedding), contrastive_loss
 
     def remove_weight_norm(self):
+        self._bump_generation()
         print('Removing weight norm...')
         for l in self.ups:
             for l_i in l:
