@@ -47,13 +47,28 @@ typedef enum {
     BVG_ERR_WORKSPACE = -5    /* workspace too small */
 } bvg_status;
 
-typedef enum { BVG_F32 = 0, BVG_BF16 = 1, BVG_I16 = 2 /* PCM output of the tail kernel only */ } bvg_dtype;
+typedef enum {
+    BVG_F32 = 0,
+    BVG_BF16 = 1,
+    BVG_I16 = 2,   /* PCM output of the tail kernel only */
+    BVG_BF16X3 = 3 /* an fp32 tensor as three bf16 pieces v = h + m + l, laid out for the split-operand tensor-core mode:
+                    * activations [.., 6*C] = [l | m | m | h | h | h], packed weights [.., 6*Cin] = [h | m | h | l | m | h]
+                    * (BVG_F32_SPLIT_TC below).  Output of bvg_split_bf16x3_nlc / bvg_activation1d_nlc_fwd / bvg_pack_*. */
+} bvg_dtype;
 
 /* bvg_precision: arithmetic mode of the convolutions.
- *   BVG_EXACT_F32 : fp32 operands, fp32 FMA accumulation (CUDA cores), accurate sin  -> the fp32 parity mode
- *   BVG_BF16_TC   : bf16 operands on tcgen05 tensor cores with fp32 TMEM accumulation; fp32 residual stream and
- *                   fp32 Activation1d arithmetic                                     -> the throughput mode   */
-typedef enum { BVG_EXACT_F32 = 0, BVG_BF16_TC = 1 } bvg_precision;
+ *   BVG_EXACT_F32    : fp32 operands, fp32 FMA accumulation on the CUDA cores, accurate sin.  The cross-check
+ *                      implementation (a plain tiled kernel); not a throughput path.
+ *   BVG_BF16_TC      : bf16 operands on tcgen05 tensor cores with fp32 TMEM accumulation; fp32 residual stream and
+ *                      fp32 Activation1d arithmetic                                  -> the throughput mode
+ *   BVG_F32_SPLIT_TC : the fp32 PARITY mode on the tensor cores (what the reference's fp32 vocoder call,
+ *                      infer_v2.py:830-831, 860, is compared with): every fp32 operand is split into three bf16 pieces
+ *                      (BVG_BF16X3) and the six significant partial products accumulate in one fp32 TMEM accumulator --
+ *                      the same tcgen05 implicit-GEMM kernel with a six times longer K axis (small terms first); what
+ *                      is dropped is below 2^-24 of a product, what remains is the tensor core's truncating fp32
+ *                      accumulation (~1e-6..1e-5 of a layer's output for the deepest K).  fp32 residual stream, accurate sin.  In the standalone conv entry points the
+ *                      operands are BVG_BF16X3 tensors (x: [B, T, 6*Cin], w_packed from bvg_pack_* with dtype BVG_BF16X3). */
+typedef enum { BVG_EXACT_F32 = 0, BVG_BF16_TC = 1, BVG_F32_SPLIT_TC = 2 } bvg_precision;
 
 #define BVG_MAX_STAGES 8
 #define BVG_MAX_KERNELS 4
@@ -91,7 +106,8 @@ BVG_API int bvg_init(int device);
 BVG_API int bvg_activation1d_fwd(const void* x, void* y, const float* alpha_log, const float* beta_log, int64_t B, int64_t C,
                          int64_t T, int64_t x_stride_b, int64_t x_stride_c, int dtype, int precise, void* stream);
 
-/* nlc layout, dense.  C % 8 == 0.  in/out dtypes independent (fp32 residual stream in, bf16 MMA operand out). */
+/* nlc layout, dense.  C % 8 == 0.  in/out dtypes independent (fp32 residual stream in, bf16 MMA operand out); with an fp32
+ * input y_dtype may also be BVG_BF16X3: y is then the split operand tensor [B, T, 6*C] of BVG_F32_SPLIT_TC. */
 BVG_API int bvg_activation1d_nlc_fwd(const void* x, int x_dtype, void* y, int y_dtype, const float* alpha_log,
                              const float* beta_log, int64_t B, int64_t T, int64_t C, int precise, void* stream);
 
@@ -110,7 +126,8 @@ BVG_API int bvg_activation1d_nlc_multi_fwd(const void* x, int x_dtype, void* con
 /* w[r, :] = g[r] * v[r, :] / ||v[r, :]||_2  (torch._weight_norm(v, g, dim=0)); rows = dim 0, row_len = rest. */
 BVG_API int bvg_fold_weight_norm(const float* v, const float* g, float* w, int64_t rows, int64_t row_len, void* stream);
 
-/* Conv1d weight [Cout, Cin, k] fp32 -> tap-major K-major [k][Cout][Cin] in `dtype` (bf16 for BVG_BF16_TC). */
+/* Conv1d weight [Cout, Cin, k] fp32 -> tap-major K-major [k][Cout][Cin] in `dtype` (bf16 for BVG_BF16_TC, fp32 for
+ * BVG_EXACT_F32; BVG_BF16X3 for BVG_F32_SPLIT_TC: [k][Cout][6*Cin] bf16, weight term order). */
 BVG_API int bvg_pack_conv1d_weight(const float* w, void* out, int64_t Cout, int64_t Cin, int64_t k, int dtype, void* stream);
 
 /* ConvTranspose1d weight [Cin, Cout, K] fp32 -> polyphase [K/u][u*Cout][Cin]: row n = r*Cout + co of tap j holds
@@ -118,6 +135,10 @@ BVG_API int bvg_pack_conv1d_weight(const float* w, void* out, int64_t Cout, int6
  * No zero-stuffed tensor is ever formed (north_star (c)).  K % u == 0. */
 BVG_API int bvg_pack_convtranspose1d_weight(const float* w, void* out, int64_t Cin, int64_t Cout, int64_t K, int64_t u,
                                     int dtype, void* stream);
+
+/* fp32 [rows, C] -> BVG_BF16X3 [rows, 6*C] (activation term order), C % 4 == 0: the operand split of BVG_F32_SPLIT_TC for
+ * tensors no Activation1d produced (the mel, conv_pre's output, the stage sums feeding the transposed convs). */
+BVG_API int bvg_split_bf16x3_nlc(const float* x, void* y_bf16x3, int64_t rows, int64_t C, void* stream);
 
 /* layout changes at the path's edges */
 BVG_API int bvg_ncl_to_nlc(const void* x, int x_dtype, int64_t x_stride_b, int64_t x_stride_c, void* y, int y_dtype, int64_t B,

@@ -13,8 +13,9 @@ LIB_PATH = os.path.join(_HERE, "libbvg.so")
 if os.environ.get("BVG_LIB_PATH"):  # developer A/B of kernel build variants (tools/build_variant.sh)
     LIB_PATH = os.environ["BVG_LIB_PATH"]
 
-BVG_F32, BVG_BF16 = 0, 1
-BVG_EXACT_F32, BVG_BF16_TC = 0, 1
+BVG_F32, BVG_BF16, BVG_I16, BVG_BF16X3 = 0, 1, 2, 3
+BVG_EXACT_F32, BVG_BF16_TC, BVG_F32_SPLIT_TC = 0, 1, 2
+SPLIT_TERMS = 6  # term slots of a BVG_BF16X3 tensor (include/bvg.h)
 MAX_STAGES, MAX_KERNELS, MAX_DILATIONS, MAX_PHASES = 8, 4, 4, 8
 
 c_i64, c_int, c_f32, c_vp, c_sz = C.c_int64, C.c_int, C.c_float, C.c_void_p, C.c_size_t
@@ -74,6 +75,7 @@ SIGNATURES = {
     "bvg_fold_weight_norm": (c_int, [c_vp, c_vp, c_vp, c_i64, c_i64, c_vp]),
     "bvg_pack_conv1d_weight": (c_int, [c_vp, c_vp, c_i64, c_i64, c_i64, c_int, c_vp]),
     "bvg_pack_convtranspose1d_weight": (c_int, [c_vp, c_vp, c_i64, c_i64, c_i64, c_i64, c_int, c_vp]),
+    "bvg_split_bf16x3_nlc": (c_int, [c_vp, c_vp, c_i64, c_i64, c_vp]),
     "bvg_ncl_to_nlc": (c_int, [c_vp, c_int, c_i64, c_i64, c_vp, c_int, c_i64, c_i64, c_i64, c_vp]),
     "bvg_nlc_to_ncl": (c_int, [c_vp, c_int, c_vp, c_int, c_i64, c_i64, c_i64, c_vp]),
     "bvg_conv1d_nlc_fwd": (c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_i64, c_i64, c_i64, c_int, c_int,

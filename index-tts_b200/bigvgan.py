@@ -80,6 +80,13 @@ def _fingerprint(tensors):
     return tuple((t.data_ptr(), t._version, t.device.index) for t in tensors)
 
 
+def _to_operand(x_ncl: torch.Tensor, prec: int) -> torch.Tensor:
+    """``[B, C, T]`` tensor -> the channels-last conv operand of precision ``prec`` (bf16, fp32 or the bf16x3 split)."""
+    if prec == _lib.BVG_F32_SPLIT_TC:
+        return ops.split_bf16x3(ops.ncl_to_nlc(x_ncl, torch.float32))
+    return ops.ncl_to_nlc(x_ncl, torch.bfloat16 if prec == _lib.BVG_BF16_TC else torch.float32)
+
+
 class Conv1d(nn.Conv1d):
     """``nn.Conv1d`` as a parameter container; ``forward`` runs the libbvg implicit-GEMM kernel ([B,C,T] in/out).
     Only what the generator uses is supported: stride 1, zeros 'same' padding, groups 1."""
@@ -99,8 +106,7 @@ class Conv1d(nn.Conv1d):
         if self.out_channels % 8 != 0:  # conv_post (C -> 1): the dedicated tail kernel without the clamp is not exposed
             raise NotImplementedError("libbvg Conv1d: out_channels must be a multiple of 8 (conv_post is fused into "
                                       "BigVGAN.forward)")
-        op_dtype = torch.bfloat16 if prec == _lib.BVG_BF16_TC else torch.float32
-        xn = ops.ncl_to_nlc(x.float() if x.dtype not in (torch.float32, torch.bfloat16) else x, op_dtype)
+        xn = _to_operand(x.float() if x.dtype not in (torch.float32, torch.bfloat16) else x, prec)
         bias = None if self.bias is None else self.bias.detach().float().contiguous()
         y = ops.conv1d_nlc(xn, self.packed(prec), bias, d, prec)
         return ops.nlc_to_ncl(y, x.dtype if x.dtype in (torch.float32, torch.bfloat16) else torch.float32)
@@ -122,8 +128,7 @@ class ConvTranspose1d(nn.ConvTranspose1d):
                 self.output_padding[0] != 0 or self.dilation[0] != 1:
             raise NotImplementedError("libbvg ConvTranspose1d: K % stride == 0 and padding (K-stride)/2 only")
         prec = ops.precision_code(self.bvg_precision or DEFAULT_PRECISION)
-        op_dtype = torch.bfloat16 if prec == _lib.BVG_BF16_TC else torch.float32
-        xn = ops.ncl_to_nlc(x, op_dtype)
+        xn = _to_operand(x, prec)
         bias = None if self.bias is None else self.bias.detach().float().contiguous()
         y = ops.convtranspose1d_nlc(xn, self.packed(prec), bias, K, u, prec)
         return ops.nlc_to_ncl(y, x.dtype if x.dtype in (torch.float32, torch.bfloat16) else torch.float32)
@@ -175,7 +180,7 @@ class AMPBlock1(torch.nn.Module):
     def forward(self, x):
         prec = _block_precision(self)
         tc = prec == _lib.BVG_BF16_TC
-        op_dtype = torch.bfloat16 if tc else torch.float32
+        op_dtype = ops.operand_dtype(prec)
         xr = ops.ncl_to_nlc(x, torch.float32)  # fp32 residual stream
         acts1, acts2 = self.activations[::2], self.activations[1::2]
         for c1, c2, a1, a2 in zip(self.convs1, self.convs2, acts1, acts2):
@@ -215,7 +220,7 @@ class AMPBlock2(torch.nn.Module):
     def forward(self, x):
         prec = _block_precision(self)
         tc = prec == _lib.BVG_BF16_TC
-        op_dtype = torch.bfloat16 if tc else torch.float32
+        op_dtype = ops.operand_dtype(prec)
         xr = ops.ncl_to_nlc(x, torch.float32)
         for c, a in zip(self.convs, self.activations):
             al, be = (t.float().contiguous() for t in a.log_params())
@@ -671,9 +676,10 @@ class BigVGAN(
         h (AttrDict): hyper-parameters (``config.json``); mutated like the reference: ``h["use_cuda_kernel"]``.
         use_cuda_kernel (bool): accepted and stored; both values run the sm_100a kernels (no torch path exists).
 
-    Extra (not in the reference): ``set_precision("bf16" | "fp32")``; default from ``$BVG_PRECISION`` or "bf16"
-    (bf16 tensor-core convs with fp32 accumulation / residual stream / activation math; "fp32" is the exact
-    parity mode).
+    Extra (not in the reference): ``set_precision("bf16" | "fp32" | "fp32_simt")``; default from ``$BVG_PRECISION`` or
+    "bf16" (bf16 tensor-core convs with fp32 accumulation / residual stream / activation math).  "fp32" is the parity mode
+    for the reference's fp32 vocoder call (infer_v2.py:830-831, 860): the same tcgen05 kernels with every operand split
+    into three bf16 pieces (fp32-exact products, fp32 accumulation); "fp32_simt" is its CUDA-core cross-check.
     """
 
     def __init__(self, h: AttrDict, use_cuda_kernel: bool = False):

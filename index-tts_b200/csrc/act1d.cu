@@ -30,6 +30,12 @@
 
 namespace bvg {
 
+// act1d_umma.cu: both FIRs on the tensor cores (fast-sin mode only); positive return = shape not taken
+int activation1d_nlc_umma(const void* x, int x_dtype, void* y, int y_dtype, const float* alpha, const float* beta, int64_t B,
+                          int64_t T, int64_t C, cudaStream_t st);
+bool act_umma_requested();
+int activation1d_umma_init();
+
 __device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) { return __ffma2_rn(a, b, c); }
 __device__ __forceinline__ float2 fmul2(float2 a, float2 b) { return __fmul2_rn(a, b); }
 __device__ __forceinline__ float2 fadd2(float2 a, float2 b) { return __fadd2_rn(a, b); }
@@ -76,7 +82,7 @@ struct PairIO;
 template <>
 struct PairIO<float> {
     static __device__ __forceinline__ float2 load(const float* p) { return __ldg(reinterpret_cast<const float2*>(p)); }
-    static __device__ __forceinline__ void store(float* p, float2 v) { *reinterpret_cast<float2*>(p) = v; }
+    static __device__ __forceinline__ void store(float* p, float2 v, int64_t) { *reinterpret_cast<float2*>(p) = v; }
 };
 template <>
 struct PairIO<__nv_bfloat16> {
@@ -84,10 +90,38 @@ struct PairIO<__nv_bfloat16> {
         unsigned int raw = __ldg(reinterpret_cast<const unsigned int*>(p));
         return make_float2(__uint_as_float(raw << 16), __uint_as_float(raw & 0xffff0000u));
     }
-    static __device__ __forceinline__ void store(__nv_bfloat16* p, float2 v) {
+    static __device__ __forceinline__ void store(__nv_bfloat16* p, float2 v, int64_t) {
         *reinterpret_cast<__nv_bfloat162*>(p) = __float22bfloat162_rn(v);
     }
 };
+// bf16x3 split output (fp32 parity mode on the tensor cores, bvg_common.cuh): an output row holds the six term slots
+// [l | m | m | h | h | h] of C channels each, so a row is 12*C bytes and slot t of this channel pair is t * row_bytes / 6
+// bytes further.  Output-only type.
+struct Split6 {
+    uint8_t bytes[12];
+};
+static_assert(sizeof(Split6) == 12, "Split6 must be 12 bytes: row pitch = C * sizeof(TOut)");
+template <>
+struct PairIO<Split6> {
+    static __device__ __forceinline__ void store(Split6* p, float2 v, int64_t row_bytes) {
+        const Bf16x3 a = split_bf16x3(v.x), b = split_bf16x3(v.y);
+        const __nv_bfloat162 h = __halves2bfloat162(a.h, b.h), m = __halves2bfloat162(a.m, b.m),
+                             l = __halves2bfloat162(a.l, b.l);
+        const int64_t slot = row_bytes / BVG_SPLIT_TERMS;  // C * 2 bytes
+        uint8_t* q = reinterpret_cast<uint8_t*>(p);
+        *reinterpret_cast<__nv_bfloat162*>(q) = l;
+        *reinterpret_cast<__nv_bfloat162*>(q + slot) = m;
+        *reinterpret_cast<__nv_bfloat162*>(q + 2 * slot) = m;
+        *reinterpret_cast<__nv_bfloat162*>(q + 3 * slot) = h;
+        *reinterpret_cast<__nv_bfloat162*>(q + 4 * slot) = h;
+        *reinterpret_cast<__nv_bfloat162*>(q + 5 * slot) = h;
+    }
+};
+// byte offset of channel `ch` inside an output row
+template <typename TOut>
+__device__ __forceinline__ int64_t out_ch_bytes(int ch) { return static_cast<int64_t>(ch) * static_cast<int64_t>(sizeof(TOut)); }
+template <>
+__device__ __forceinline__ int64_t out_ch_bytes<Split6>(int ch) { return static_cast<int64_t>(ch) * 2; }
 
 // ------------------------------------------------------------------------------------------------------------
 // channels-last kernel
@@ -182,7 +216,7 @@ __device__ __forceinline__ void act1d_nlc_body(float2 (&xw)[7], float2 (&acc)[NH
             ym2 = ffma2(G1, o, ym2);
             if (!FIRST || s == 6) {
                 const int i = g - 6;  // output row relative to t0
-                if (!EDGE || i < e.n_out) PairIO<TOut>::store(reinterpret_cast<TOut*>(yp + ydelta[h]), ym3);
+                if (!EDGE || i < e.n_out) PairIO<TOut>::store(reinterpret_cast<TOut*>(yp + ydelta[h]), ym3, row_bytes);
             }
         }
         yp += row_bytes;  // running byte pointer (row g - 6 of the segment): one 64-bit add per row, no multiply per store
@@ -251,7 +285,7 @@ act1d_nlc_kernel(const TIn* __restrict__ x, TOut* __restrict__ y, const float* _
     const int64_t b = blockIdx.z;
     const int64_t t0 = seg * L;
     const TIn* xb = x + (b * T) * C + 2 * pair;
-    TOut* yb = y + (b * T) * C + 2 * pair;
+    TOut* yb = reinterpret_cast<TOut*>(reinterpret_cast<uint8_t*>(y + (b * T) * C) + out_ch_bytes<TOut>(2 * pair));
     const SnakeCoef coef = make_coef<PRECISE>(alpha[2 * pair], alpha[2 * pair + 1], beta[2 * pair], beta[2 * pair + 1]);
     // the segment's loads touch rows t0-6 .. t0+L+5 (the last 7-row prefetch is skipped)
     const bool interior = (t0 >= 6) && (t0 + L + 6 <= T);
@@ -399,7 +433,9 @@ act1d_nlc_tma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_con
             coef[h] = make_coef<PRECISE>(hd.alpha[h][ch], hd.alpha[h][ch + 1], hd.beta[h][ch], hd.beta[h][ch + 1]);
             ydelta[h] = static_cast<const uint8_t*>(hd.y[h]) - static_cast<const uint8_t*>(hd.y[0]);
         }
-        TOut* yrel = static_cast<TOut*>(hd.y[0]) + (static_cast<int64_t>(b) * T + t0) * C + ch;
+        TOut* yrel = reinterpret_cast<TOut*>(
+            reinterpret_cast<uint8_t*>(static_cast<TOut*>(hd.y[0]) + (static_cast<int64_t>(b) * T + t0) * C) +
+            out_ch_bytes<TOut>(ch));
         const int64_t row_bytes = static_cast<int64_t>(C) * static_cast<int64_t>(sizeof(TOut));
         uint8_t* yp = reinterpret_cast<uint8_t*>(yrel) - 6 * row_bytes;  // row -6: never dereferenced before row 0
 
@@ -849,13 +885,14 @@ int activation1d_init() {
     for (int precise = 0; precise < 2; ++precise) {
         int rc = act_tma_attrs<float, __nv_bfloat16, 1>(precise);
         if (rc == BVG_OK) rc = act_tma_attrs<float, float, 1>(precise);
+        if (rc == BVG_OK) rc = act_tma_attrs<float, Split6, 1>(precise);
         if (rc == BVG_OK) rc = act_tma_attrs<__nv_bfloat16, __nv_bfloat16, 1>(precise);
         if (rc == BVG_OK) rc = act_tma_attrs<__nv_bfloat16, float, 1>(precise);
         if (rc == BVG_OK) rc = act_tma_attrs<float, __nv_bfloat16, 3>(precise);
         if (rc == BVG_OK) rc = act_tma_attrs<float, float, 3>(precise);
         if (rc != BVG_OK) return rc;
     }
-    return BVG_OK;
+    return activation1d_umma_init();
 }
 
 static bool act_legacy_requested() {
@@ -888,9 +925,15 @@ int activation1d_nlc(const void* x, int x_dtype, void* y, int y_dtype, const flo
     BVG_REQUIRE(C % 2 == 0, BVG_ERR_UNSUPPORTED, "activation1d_nlc: C=%lld must be even", (long long)C);
     BVG_REQUIRE(B <= 65535, BVG_ERR_UNSUPPORTED, "activation1d_nlc: B=%lld > 65535", (long long)B);
     if (B == 0 || T == 0) return BVG_OK;
+    if (!precise && act_umma_requested()) {  // throughput mode: the tensor-core kernel (act1d_umma.cu)
+        const int rc = activation1d_nlc_umma(x, x_dtype, y, y_dtype, alpha, beta, B, T, C, st);
+        if (rc <= 0) return rc;
+    }
     if (x_dtype == BVG_F32 && y_dtype == BVG_BF16)
         return launch_nlc_any<float, __nv_bfloat16>(x, y, alpha, beta, B, T, C, precise, st);
     if (x_dtype == BVG_F32 && y_dtype == BVG_F32) return launch_nlc_any<float, float>(x, y, alpha, beta, B, T, C, precise, st);
+    if (x_dtype == BVG_F32 && y_dtype == BVG_BF16X3)  // fp32 parity mode on the tensor cores: split output [B, T, 6*C]
+        return launch_nlc_any<float, Split6>(x, y, alpha, beta, B, T, C, precise, st);
     if (x_dtype == BVG_BF16 && y_dtype == BVG_BF16)
         return launch_nlc_any<__nv_bfloat16, __nv_bfloat16>(x, y, alpha, beta, B, T, C, precise, st);
     if (x_dtype == BVG_BF16 && y_dtype == BVG_F32)
@@ -933,7 +976,10 @@ int activation1d_nlc_multi(const void* x, int x_dtype, void* const* ys, int y_dt
                 "activation1d_nlc_multi: bad shape B=%lld T=%lld C=%lld", (long long)B, (long long)T, (long long)C);
     if (B == 0 || T == 0) return BVG_OK;
     int h0 = 0;
-    for (; h0 + 3 <= n_heads; h0 += 3) {
+    // fast-sin mode on shapes the tensor-core kernel takes: one launch per head (three of those beat the shared-up-sampler
+    // SIMT kernel, and results stay bit-identical to single calls by construction)
+    const bool per_head = !precise && act_umma_requested() && C % 8 == 0;
+    for (; !per_head && h0 + 3 <= n_heads; h0 += 3) {
         int rc;
         if (x_dtype == BVG_F32 && y_dtype == BVG_BF16)
             rc = launch_nlc_heads3<float, __nv_bfloat16>(x, ys + h0, alphas + h0, betas + h0, B, T, C, precise, st);

@@ -22,6 +22,7 @@ int transpose_any(const void* src, int src_dtype, void* dst, int dst_dtype, int6
                   int64_t sr, cudaStream_t st);
 int add_channel_vector(const void* x, int x_dtype, const float* v, void* y, int y_dtype, int64_t B, int64_t T, int64_t C,
                        cudaStream_t st);
+int split_rows(const float* x, void* y, int64_t rows, int64_t C, cudaStream_t st);
 
 static int conv_dispatch(int precision, const void* x, const void* w, const float* bias, const float* residual,
                          const float* accum, float* y_f32, void* y_bf16, int64_t B, int64_t T, int64_t Cin, int64_t N,
@@ -30,6 +31,13 @@ static int conv_dispatch(int precision, const void* x, const void* w, const floa
     if (precision == BVG_BF16_TC)
         return conv_umma_launch(x, w, bias, residual, accum, y_f32, y_bf16, B, T, Cin, N, cout_phase, taps, dil, tap_base,
                                 num_phases, out_scale, st, cond);
+    if (precision == BVG_F32_SPLIT_TC) {
+        // fp32 parity mode: x and w are bf16x3 split tensors (six term slots of Cin channels each on the K axis of the
+        // same kernel, bvg_common.cuh); fp32 accumulation in TMEM, fp32 outputs only
+        BVG_REQUIRE(y_bf16 == nullptr && y_f32 != nullptr, BVG_ERR_INVALID, "split-operand conv: the output is fp32");
+        return conv_umma_launch(x, w, bias, residual, accum, y_f32, nullptr, B, T, Cin * BVG_SPLIT_TERMS, N, cout_phase, taps,
+                                dil, tap_base, num_phases, out_scale, st, cond);
+    }
     if (precision == BVG_EXACT_F32)
         return conv_simt_launch(x, w, bias, residual, accum, y_f32, y_bf16, B, T, Cin, N, cout_phase, taps, dil, tap_base,
                                 num_phases, out_scale, st, cond);
@@ -113,14 +121,16 @@ static int make_plan(const bvg_model_desc* m, int64_t B, int64_t T_mel, Plan* pl
     BVG_REQUIRE(m->num_stages >= 1 && m->num_stages <= BVG_MAX_STAGES && m->num_kernels >= 1 &&
                     m->num_kernels <= BVG_MAX_KERNELS && m->num_dilations >= 1 && m->num_dilations <= BVG_MAX_DILATIONS,
                 BVG_ERR_UNSUPPORTED, "model descriptor: stages/kernels/dilations out of range");
-    BVG_REQUIRE(m->precision == BVG_EXACT_F32 || m->precision == BVG_BF16_TC, BVG_ERR_UNSUPPORTED,
-                "model descriptor: unknown precision %d", m->precision);
+    BVG_REQUIRE(m->precision == BVG_EXACT_F32 || m->precision == BVG_BF16_TC || m->precision == BVG_F32_SPLIT_TC,
+                BVG_ERR_UNSUPPORTED, "model descriptor: unknown precision %d", m->precision);
     BVG_REQUIRE(m->num_mels % 8 == 0 && (m->upsample_initial_channel >> m->num_stages) % 8 == 0, BVG_ERR_UNSUPPORTED,
                 "channel counts must be multiples of 8 (num_mels=%d, last stage %d)", m->num_mels,
                 m->upsample_initial_channel >> m->num_stages);
     pl->B = B;
     pl->T_mel = T_mel;
-    pl->op_es = m->precision == BVG_BF16_TC ? 2 : 4;
+    // bytes per conv-operand element: bf16, bf16x3 split (six term slots), fp32
+    pl->op_es = m->precision == BVG_BF16_TC ? 2 : (m->precision == BVG_F32_SPLIT_TC ? 2 * BVG_SPLIT_TERMS : 4);
+    const size_t y1_es = m->precision == BVG_BF16_TC ? 2 : 4;  // conv1 -> activation intermediate
     BVG_REQUIRE(m->resblock >= 0 && m->resblock <= 2, BVG_ERR_UNSUPPORTED, "model descriptor: unknown resblock type %d",
                 m->resblock);
     int64_t T = T_mel, E = B * T_mel * m->upsample_initial_channel;
@@ -139,7 +149,7 @@ static int make_plan(const bvg_model_desc* m, int64_t B, int64_t T_mel, Plan* pl
     for (int j = 0; j < m->num_kernels; ++j) {
         pl->off_r[j] = o;  o += align256((size_t)E * 4);
         pl->off_a[j] = o;  o += align256((size_t)E * pl->op_es);
-        pl->off_y1[j] = o; o += align256((size_t)E * pl->op_es);
+        pl->off_y1[j] = o; o += align256((size_t)E * y1_es);
     }
     pl->total = o;
     return BVG_OK;
@@ -288,7 +298,9 @@ static int forward_impl(const bvg_model_desc* m, const float* mel, int mel_layou
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const int prec = m->precision;
     const bool tc = prec == BVG_BF16_TC;
-    const int op_dt = tc ? BVG_BF16 : BVG_F32;
+    const bool split = prec == BVG_F32_SPLIT_TC;  // fp32 parity mode on the tensor cores (bf16x3 split operands)
+    const int op_dt = tc ? BVG_BF16 : (split ? BVG_BF16X3 : BVG_F32);
+    const int y1_dt = tc ? BVG_BF16 : BVG_F32;
     const int precise = tc ? 0 : 1;
     uint8_t* ws = static_cast<uint8_t*>(workspace);
     void* mel_nlc = ws + pl.off_mel;
@@ -310,7 +322,15 @@ static int forward_impl(const bvg_model_desc* m, const float* mel, int mel_layou
     // mel [B, num_mels, T] -> [B, T, num_mels] in the operand dtype (an nlc input only changes dtype)
     {
     ProfScope ps(BVG_K_LAYOUT, -1, m->num_mels, m->num_mels, 0, 0, B * T_mel, 0.0, 0.0, st);
-    if (mel_layout == 0)
+    if (split) {
+        // fp32 channels-last copy in SUM (free until the first stage ends), then the operand split
+        const float* mel32 = mel;
+        if (mel_layout == 0) {
+            rc = transpose_any(mel, BVG_F32, SUM, BVG_F32, B, m->num_mels, T_mel, mel_stride_b, mel_stride_c, st);
+            mel32 = SUM;
+        }
+        if (rc == BVG_OK) rc = split_rows(mel32, mel_nlc, B * T_mel, m->num_mels, st);
+    } else if (mel_layout == 0)
         rc = transpose_any(mel, BVG_F32, mel_nlc, op_dt, B, m->num_mels, T_mel, mel_stride_b, mel_stride_c, st);
     else if (tc)
         rc = add_channel_vector(mel, BVG_F32, nullptr, mel_nlc, op_dt, B, T_mel, m->num_mels, st);
@@ -319,24 +339,31 @@ static int forward_impl(const bvg_model_desc* m, const float* mel, int mel_layou
     }
     if (rc != BVG_OK) return rc;
     // conv_pre (bigvgan.py:362): output feeds the first transposed conv directly -> operand dtype
+    const bool cond_pre = cond != nullptr && cond[0] != nullptr;
     {
         const bvg_conv_desc& c = m->conv_pre;
         ProfScope ps(BVG_K_CONV1D, -1, c.cin, c.cout, c.k, 1, B * T_mel, conv_flops(c.cin, c.cout, c.k, (double)B * T_mel),
                      conv_bytes(c.cin, c.cout, c.k, (double)B * T_mel, false), st);
         BVG_REQUIRE(c.cin == m->num_mels && c.cout == m->upsample_initial_channel, BVG_ERR_INVALID, "conv_pre: channel mismatch");
-        const bool cond_pre = cond != nullptr && cond[0] != nullptr;
         // conditioned (v1, indextts/BigVGAN/models.py:236): the per-utterance vector rides in the conv epilogue as a second
         // bias (one rounding to the operand dtype).  BVG_COND_FUSED=0: fp32 result into X and a separate add kernel.
-        float* pre_f32 = (cond_pre && !fused_cond) ? X : (tc ? nullptr : reinterpret_cast<float*>(pre));
+        // Split mode: the fp32 result goes to X and is split into the operand tensor afterwards.
+        float* pre_f32 = (split || (cond_pre && !fused_cond)) ? X : (tc ? nullptr : reinterpret_cast<float*>(pre));
         rc = conv1d(prec, mel_nlc, c.w, c.bias, nullptr, nullptr, pre_f32, pre_f32 ? nullptr : pre, B, T_mel, c.cin, c.cout,
                     c.k, 1, 1.0f, st, (cond_pre && fused_cond) ? cond[0] : nullptr);
         if (rc != BVG_OK) return rc;
     }
-    if (cond != nullptr && cond[0] != nullptr && !fused_cond) {
+    if (cond_pre && !fused_cond) {
         // x = x + cond_layer(speaker_embedding)   (indextts/BigVGAN/models.py:236)
         const double n = (double)B * T_mel * m->upsample_initial_channel;
         ProfScope ps(BVG_K_COND, -1, m->upsample_initial_channel, m->upsample_initial_channel, 0, 0, B * T_mel, n, (4.0 + es) * n, st);
-        rc = add_channel_vector(X, BVG_F32, cond[0], pre, op_dt, B, T_mel, m->upsample_initial_channel, st);
+        rc = split ? add_channel_vector(X, BVG_F32, cond[0], X, BVG_F32, B, T_mel, m->upsample_initial_channel, st)
+                   : add_channel_vector(X, BVG_F32, cond[0], pre, op_dt, B, T_mel, m->upsample_initial_channel, st);
+        if (rc != BVG_OK) return rc;
+    }
+    if (split) {
+        ProfScope ps(BVG_K_LAYOUT, -1, m->upsample_initial_channel, m->upsample_initial_channel, 0, 0, B * T_mel, 0.0, 0.0, st);
+        rc = split_rows(X, pre, B * T_mel, m->upsample_initial_channel, st);
         if (rc != BVG_OK) return rc;
     }
     const void* stage_in = pre;
@@ -421,7 +448,7 @@ static int forward_impl(const bvg_model_desc* m, const float* mel, int mel_layou
                 if (rc != BVG_OK) return rc;
                 if (!amp2) {
                     ProfScope ps(BVG_K_ACT, i, C, C, 0, 0, B * T, act_flops, act_bytes, sj);
-                    rc = activation1d_nlc(Y1, op_dt, A, op_dt, a2.alpha_log, a2.beta_log, B, T, C, precise, sj);
+                    rc = activation1d_nlc(Y1, y1_dt, A, op_dt, a2.alpha_log, a2.beta_log, B, T, C, precise, sj);
                 }
                 if (rc != BVG_OK) return rc;
                 // AMPBlock2: the block's only conv of this dilation carries the residual add (the conv the code below
@@ -451,7 +478,12 @@ static int forward_impl(const bvg_model_desc* m, const float* mel, int mel_layou
             BVG_CUDA(cudaStreamWaitEvent(st, aux->last[m->num_kernels - 1], 0));
             join_guard.joined();
         }
-        stage_in = tc ? SUMOP : static_cast<const void*>(SUM);
+        if (split && !last_stage) {  // operand split of the stage output for the next transposed conv
+            ProfScope ps(BVG_K_LAYOUT, i, C, C, 0, 0, B * T, 0.0, 0.0, st);
+            rc = split_rows(SUM, SUMOP, B * T, C, st);
+            if (rc != BVG_OK) return rc;
+        }
+        stage_in = (tc || split) ? SUMOP : static_cast<const void*>(SUM);
     }
     // activation_post -> conv_post -> clamp / tanh (bigvgan.py:378-384), fp32 in both modes
     {

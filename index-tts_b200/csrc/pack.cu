@@ -66,6 +66,74 @@ __global__ void pack_convt_kernel(const float* __restrict__ w, TOut* __restrict_
     }
 }
 
+// bf16x3 split forms of the two packings (bvg_common.cuh): out[j][n][t*Cin + ci] = term t of the same element
+__global__ void pack_conv1d_split_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ out, int64_t Cout,
+                                         int64_t Cin, int64_t k) {
+    const int64_t total = Cout * Cin * k;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t ci = i % Cin;
+        const int64_t co = (i / Cin) % Cout;
+        const int64_t j = i / (Cin * Cout);
+        const Bf16x3 s = split_bf16x3(w[(co * Cin + ci) * k + j]);
+        __nv_bfloat16* o = out + (j * Cout + co) * (BVG_SPLIT_TERMS * Cin) + ci;
+#pragma unroll
+        for (int t = 0; t < BVG_SPLIT_TERMS; ++t) o[t * Cin] = split_w_term(s, t);
+    }
+}
+
+__global__ void pack_convt_split_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ out, int64_t Cin,
+                                        int64_t Cout, int64_t K, int64_t u) {
+    const int64_t taps = K / u, p = (K - u) / 2;
+    const int64_t total = taps * u * Cout * Cin;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t ci = i % Cin;
+        const int64_t n = (i / Cin) % (u * Cout);
+        const int64_t j = i / (Cin * u * Cout);
+        const int64_t r = n / Cout, co = n % Cout;
+        const int64_t kk = (r + p) % u + u * (taps - 1 - j);
+        const Bf16x3 s = split_bf16x3(w[(ci * Cout + co) * K + kk]);
+        __nv_bfloat16* o = out + (j * u * Cout + n) * (BVG_SPLIT_TERMS * Cin) + ci;
+#pragma unroll
+        for (int t = 0; t < BVG_SPLIT_TERMS; ++t) o[t * Cin] = split_w_term(s, t);
+    }
+}
+
+// fp32 [rows, C] -> bf16 [rows, 6*C] activation split (the tensors a conv reads that no Activation1d produced: the mel,
+// conv_pre's output, the stage sums).  One thread per channel quad; 16-byte loads, 8-byte stores.
+__global__ void split_rows_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ y, int64_t rows, int C) {
+    const int64_t quads = rows * (C / 4);
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < quads; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = i / (C / 4);
+        const int c = static_cast<int>(i - r * (C / 4)) * 4;
+        const float4 v = __ldg(reinterpret_cast<const float4*>(x + r * C + c));
+        const Bf16x3 s0 = split_bf16x3(v.x), s1 = split_bf16x3(v.y), s2 = split_bf16x3(v.z), s3 = split_bf16x3(v.w);
+        __nv_bfloat16* o = y + r * (int64_t)(BVG_SPLIT_TERMS * C) + c;
+#pragma unroll
+        for (int t = 0; t < BVG_SPLIT_TERMS; ++t) {
+            __nv_bfloat162 a = __halves2bfloat162(split_act_term(s0, t), split_act_term(s1, t));
+            __nv_bfloat162 b = __halves2bfloat162(split_act_term(s2, t), split_act_term(s3, t));
+            uint2 pk;
+            pk.x = *reinterpret_cast<unsigned int*>(&a);
+            pk.y = *reinterpret_cast<unsigned int*>(&b);
+            *reinterpret_cast<uint2*>(o + (int64_t)t * C) = pk;
+        }
+    }
+}
+
+int split_rows(const float* x, void* y, int64_t rows, int64_t C, cudaStream_t st) {
+    BVG_REQUIRE(x && y, BVG_ERR_INVALID, "split_bf16x3: null pointer");
+    BVG_REQUIRE(rows >= 0 && C > 0 && C % 4 == 0 && C < (int64_t(1) << 28), BVG_ERR_INVALID,
+                "split_bf16x3: bad shape rows=%lld C=%lld (C %% 4 == 0)", (long long)rows, (long long)C);
+    BVG_REQUIRE(reinterpret_cast<uintptr_t>(x) % 16 == 0 && reinterpret_cast<uintptr_t>(y) % 8 == 0, BVG_ERR_INVALID,
+                "split_bf16x3: x must be 16-byte and y 8-byte aligned");
+    if (rows == 0) return BVG_OK;
+    const int64_t quads = rows * (C / 4);
+    const unsigned grid = (unsigned)(ceil_div(quads, 256) < 148 * 16 ? ceil_div(quads, 256) : 148 * 16);
+    split_rows_kernel<<<grid, 256, 0, st>>>(x, static_cast<__nv_bfloat16*>(y), rows, (int)C);
+    BVG_LAUNCH_CHECK("split_rows_kernel");
+    return BVG_OK;
+}
+
 // ------------------------------------------------------------------------------------------------------------
 // [B,C,T] <-> [B,T,C] with dtype conversion, 32x32 smem tiles
 // ------------------------------------------------------------------------------------------------------------
@@ -304,6 +372,8 @@ extern "C" int bvg_pack_conv1d_weight(const float* w, void* out, int64_t Cout, i
         pack_conv1d_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(w, static_cast<__nv_bfloat16*>(out), Cout, Cin, k);
     else if (dtype == BVG_F32)
         pack_conv1d_kernel<float><<<grid, 256, 0, st>>>(w, static_cast<float*>(out), Cout, Cin, k);
+    else if (dtype == BVG_BF16X3)
+        pack_conv1d_split_kernel<<<grid, 256, 0, st>>>(w, static_cast<__nv_bfloat16*>(out), Cout, Cin, k);
     else
         return set_error(BVG_ERR_UNSUPPORTED, "bvg_pack_conv1d_weight: dtype %d", dtype);
     BVG_LAUNCH_CHECK("pack_conv1d_kernel");
@@ -324,10 +394,16 @@ extern "C" int bvg_pack_convtranspose1d_weight(const float* w, void* out, int64_
         pack_convt_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(w, static_cast<__nv_bfloat16*>(out), Cin, Cout, K, u);
     else if (dtype == BVG_F32)
         pack_convt_kernel<float><<<grid, 256, 0, st>>>(w, static_cast<float*>(out), Cin, Cout, K, u);
+    else if (dtype == BVG_BF16X3)
+        pack_convt_split_kernel<<<grid, 256, 0, st>>>(w, static_cast<__nv_bfloat16*>(out), Cin, Cout, K, u);
     else
         return set_error(BVG_ERR_UNSUPPORTED, "bvg_pack_convtranspose1d_weight: dtype %d", dtype);
     BVG_LAUNCH_CHECK("pack_convt_kernel");
     return BVG_OK;
+}
+
+extern "C" int bvg_split_bf16x3_nlc(const float* x, void* y, int64_t rows, int64_t C, void* stream) {
+    return split_rows(x, y, rows, C, static_cast<cudaStream_t>(stream));
 }
 
 extern "C" int bvg_ncl_to_nlc(const void* x, int x_dtype, int64_t x_stride_b, int64_t x_stride_c, void* y, int y_dtype,

@@ -13,7 +13,9 @@ from typing import Optional
 import torch
 
 from . import _lib
-from ._lib import BVG_BF16, BVG_BF16_TC, BVG_EXACT_F32, BVG_F32, check
+from ._lib import (BVG_BF16, BVG_BF16_TC, BVG_BF16X3, BVG_EXACT_F32, BVG_F32, BVG_F32_SPLIT_TC, SPLIT_TERMS, check)
+
+BF16X3 = "bf16x3"  # out_dtype sentinel: the split operand tensor of the fp32 parity mode (a bf16 tensor [.., 6*C])
 
 _DT = {torch.float32: BVG_F32, torch.bfloat16: BVG_BF16}
 
@@ -39,11 +41,39 @@ def _dt(t: torch.Tensor, what: str) -> int:
 
 
 def precision_code(name) -> int:
-    if name in (BVG_EXACT_F32, "fp32", "float32", "exact", torch.float32):
-        return BVG_EXACT_F32
-    if name in (BVG_BF16_TC, "bf16", "bfloat16", torch.bfloat16):
+    """'bf16': tensor-core throughput mode.  'fp32': the fp32 parity mode, on the tensor cores with bf16x3 split operands
+    (BVG_F32_SPLIT_TC).  'fp32_simt': the CUDA-core cross-check implementation of the fp32 mode (BVG_EXACT_F32)."""
+    if isinstance(name, str):
+        if name in ("fp32", "float32", "exact"):
+            return BVG_F32_SPLIT_TC
+        if name in ("fp32_simt", "exact_simt"):
+            return BVG_EXACT_F32
+        if name in ("bf16", "bfloat16"):
+            return BVG_BF16_TC
+    elif name is torch.float32:
+        return BVG_F32_SPLIT_TC
+    elif name is torch.bfloat16:
         return BVG_BF16_TC
-    raise ValueError(f"unknown precision {name!r} (use 'bf16' or 'fp32')")
+    elif name in (BVG_EXACT_F32, BVG_BF16_TC, BVG_F32_SPLIT_TC):
+        return int(name)
+    raise ValueError(f"unknown precision {name!r} (use 'bf16', 'fp32' or 'fp32_simt')")
+
+
+def operand_dtype(precision: int):
+    """What a conv of this precision reads: torch.bfloat16, the BF16X3 sentinel or torch.float32."""
+    return torch.bfloat16 if precision == BVG_BF16_TC else (BF16X3 if precision == BVG_F32_SPLIT_TC else torch.float32)
+
+
+def split_bf16x3(x: torch.Tensor) -> torch.Tensor:
+    """fp32 ``[..., C]`` -> the BVG_BF16X3 operand tensor ``[..., 6*C]`` (bf16; include/bvg.h)."""
+    _require_cuda(x, "split_bf16x3")
+    x = x.float().contiguous()
+    C = x.shape[-1]
+    y = torch.empty(tuple(x.shape[:-1]) + (SPLIT_TERMS * C,), dtype=torch.bfloat16, device=x.device)
+    rows = x.numel() // max(C, 1)
+    with torch.cuda.device(x.device):
+        check(_lib.load().bvg_split_bf16x3_nlc(x.data_ptr(), y.data_ptr(), rows, C, _stream()), "bvg_split_bf16x3_nlc")
+    return y
 
 
 # ---------------------------------------------------------------------------------------------------------------
@@ -83,15 +113,21 @@ def _(x, alpha_log, beta_log, precise):
     return torch.empty_like(x, memory_format=torch.contiguous_format)
 
 
-def activation1d_nlc(x: torch.Tensor, alpha_log: torch.Tensor, beta_log: torch.Tensor, out_dtype: torch.dtype,
+def activation1d_nlc(x: torch.Tensor, alpha_log: torch.Tensor, beta_log: torch.Tensor, out_dtype,
                      precise: bool) -> torch.Tensor:
-    """Channels-last ``[B, T, C]`` variant used inside the generator."""
+    """Channels-last ``[B, T, C]`` variant used inside the generator.  ``out_dtype`` may be ``ops.BF16X3`` (fp32 input
+    only): the result is then the split operand tensor ``[B, T, 6*C]`` of the fp32 parity mode."""
     _require_cuda(x, "activation1d_nlc")
     x = x.contiguous()
     B, T, C = x.shape
-    y = torch.empty((B, T, C), dtype=out_dtype, device=x.device)
+    if out_dtype == BF16X3:
+        y = torch.empty((B, T, SPLIT_TERMS * C), dtype=torch.bfloat16, device=x.device)
+        y_code = BVG_BF16X3
+    else:
+        y = torch.empty((B, T, C), dtype=out_dtype, device=x.device)
+        y_code = _DT[out_dtype]
     with torch.cuda.device(x.device):
-        check(_lib.load().bvg_activation1d_nlc_fwd(x.data_ptr(), _dt(x, "activation1d_nlc"), y.data_ptr(), _DT[out_dtype],
+        check(_lib.load().bvg_activation1d_nlc_fwd(x.data_ptr(), _dt(x, "activation1d_nlc"), y.data_ptr(), y_code,
                                                    alpha_log.data_ptr(), beta_log.data_ptr(), B, T, C,
                                                    int(bool(precise)), _stream()), "bvg_activation1d_nlc_fwd")
     return y
@@ -161,10 +197,15 @@ def pack_conv1d_weight(w: torch.Tensor, precision: int) -> torch.Tensor:
     _require_cuda(w, "pack_conv1d_weight")
     w = w.detach().float().contiguous()
     Cout, Cin, k = w.shape
-    dt = torch.bfloat16 if precision == BVG_BF16_TC else torch.float32
-    out = torch.empty((k, Cout, Cin), dtype=dt, device=w.device)
+    if precision == BVG_F32_SPLIT_TC:
+        out = torch.empty((k, Cout, SPLIT_TERMS * Cin), dtype=torch.bfloat16, device=w.device)
+        code = BVG_BF16X3
+    else:
+        dt = torch.bfloat16 if precision == BVG_BF16_TC else torch.float32
+        out = torch.empty((k, Cout, Cin), dtype=dt, device=w.device)
+        code = _DT[dt]
     with torch.cuda.device(w.device):
-        check(_lib.load().bvg_pack_conv1d_weight(w.data_ptr(), out.data_ptr(), Cout, Cin, k, _DT[dt], _stream()),
+        check(_lib.load().bvg_pack_conv1d_weight(w.data_ptr(), out.data_ptr(), Cout, Cin, k, code, _stream()),
               "bvg_pack_conv1d_weight")
     return out
 
@@ -174,10 +215,15 @@ def pack_convtranspose1d_weight(w: torch.Tensor, stride: int, precision: int) ->
     _require_cuda(w, "pack_convtranspose1d_weight")
     w = w.detach().float().contiguous()
     Cin, Cout, K = w.shape
-    dt = torch.bfloat16 if precision == BVG_BF16_TC else torch.float32
-    out = torch.empty((K // stride, stride * Cout, Cin), dtype=dt, device=w.device)
+    if precision == BVG_F32_SPLIT_TC:
+        out = torch.empty((K // stride, stride * Cout, SPLIT_TERMS * Cin), dtype=torch.bfloat16, device=w.device)
+        code = BVG_BF16X3
+    else:
+        dt = torch.bfloat16 if precision == BVG_BF16_TC else torch.float32
+        out = torch.empty((K // stride, stride * Cout, Cin), dtype=dt, device=w.device)
+        code = _DT[dt]
     with torch.cuda.device(w.device):
-        check(_lib.load().bvg_pack_convtranspose1d_weight(w.data_ptr(), out.data_ptr(), Cin, Cout, K, stride, _DT[dt],
+        check(_lib.load().bvg_pack_convtranspose1d_weight(w.data_ptr(), out.data_ptr(), Cin, Cout, K, stride, code,
                                                           _stream()), "bvg_pack_convtranspose1d_weight")
     return out
 
@@ -194,9 +240,13 @@ def conv1d_nlc(x: torch.Tensor, w_packed: torch.Tensor, bias: Optional[torch.Ten
     k, Cout, Cin2 = w_packed.shape
     if Cin2 != Cin:
         raise _lib.BvgError(f"conv1d_nlc: weight has {Cin2} input channels, x has {Cin}")
-    want = torch.bfloat16 if precision == BVG_BF16_TC else torch.float32
+    want = torch.float32 if precision == BVG_EXACT_F32 else torch.bfloat16
     if x.dtype != want or w_packed.dtype != want:
         raise _lib.BvgError(f"conv1d_nlc: operands must be {want} for this precision (x {x.dtype}, w {w_packed.dtype})")
+    if precision == BVG_F32_SPLIT_TC:  # operands are BVG_BF16X3 tensors: the C ABI takes the logical channel count
+        if Cin % SPLIT_TERMS or out_bf16:
+            raise _lib.BvgError("conv1d_nlc: split-operand mode needs [B, T, 6*Cin] operands and has fp32 outputs only")
+        Cin //= SPLIT_TERMS
     y32 = torch.empty((B, T, Cout), dtype=torch.float32, device=x.device) if out_f32 else None
     y16 = torch.empty((B, T, Cout), dtype=torch.bfloat16, device=x.device) if out_bf16 else None
     with torch.cuda.device(x.device):
@@ -217,6 +267,10 @@ def convtranspose1d_nlc(x: torch.Tensor, w_packed: torch.Tensor, bias: Optional[
     Cout = N // stride
     if Cin2 != Cin or taps * stride != K:
         raise _lib.BvgError("convtranspose1d_nlc: packed weight does not match x / K / stride")
+    if precision == BVG_F32_SPLIT_TC:
+        if Cin % SPLIT_TERMS or out_bf16:
+            raise _lib.BvgError("convtranspose1d_nlc: split-operand mode needs [B, T, 6*Cin] operands, fp32 outputs only")
+        Cin //= SPLIT_TERMS
     y32 = torch.empty((B, Tin * stride, Cout), dtype=torch.float32, device=x.device) if out_f32 else None
     y16 = torch.empty((B, Tin * stride, Cout), dtype=torch.bfloat16, device=x.device) if out_bf16 else None
     with torch.cuda.device(x.device):

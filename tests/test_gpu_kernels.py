@@ -221,6 +221,79 @@ def test_conv1d_tcgen05_bf16(ops, case):
     assert rel_err(ref, np.transpose(y16.float().cpu().numpy(), (0, 2, 1))) < 2.0 ** -8
 
 
+def test_split_bf16x3_is_exact(ops):
+    """fp32 -> three bf16 pieces: h + m + l == x exactly (in fp64), term slots in the documented order."""
+    rng = np.random.default_rng(12)
+    x = (rng.standard_normal((3, 37, 24)) * np.exp(rng.uniform(-12, 12, (3, 37, 24)))).astype(np.float32)
+    y = ops.split_bf16x3(_t(x)).float().cpu().numpy().astype(np.float64)
+    assert y.shape == (3, 37, 144)
+    t = [y[..., 24 * i:24 * (i + 1)] for i in range(6)]
+    l, m, h = t[0], t[1], t[3]  # activation slots [l | m | m | h | h | h]
+    np.testing.assert_array_equal(t[2], m); np.testing.assert_array_equal(t[4], h); np.testing.assert_array_equal(t[5], h)
+    np.testing.assert_array_equal(h + m + l, x.astype(np.float64))
+    # weight term order [h | m | h | l | m | h]
+    w = rng.standard_normal((8, 16, 3)).astype(np.float32)
+    p = ops.pack_conv1d_weight(_t(w), 2).float().cpu().numpy().astype(np.float64)
+    assert p.shape == (3, 8, 96)
+    s = [p[..., 16 * i:16 * (i + 1)] for i in range(6)]
+    np.testing.assert_array_equal(s[0] + s[1] + s[3], np.transpose(w, (2, 0, 1)).astype(np.float64))
+    np.testing.assert_array_equal(s[2], s[0]); np.testing.assert_array_equal(s[4], s[1]); np.testing.assert_array_equal(s[5], s[0])
+
+
+CONVT_CASES_SPLIT = [(2, 1536, 768, 20, 8, 4), (1, 384, 192, 130, 4, 2), (1, 48, 24, 257, 4, 2), (1, 16, 8, 1, 8, 4)]
+
+
+@pytest.mark.parametrize("case", CONV_CASES)
+def test_conv1d_split_f32_on_tcgen05(ops, case):
+    """BVG_F32_SPLIT_TC conv (bf16x3 split operands on the tensor cores, fp32 TMEM accumulation) on FULL fp32 operands vs
+    the fp64 oracle incl. bias + residual + scale + accum: the same <= 1e-5 of max |y| as the CUDA-core exact kernel, and
+    within 4e-6 of that kernel's own result."""
+    B, Cin, Cout, T, k, d = case
+    rng = np.random.default_rng(hash(case) % 2 ** 31)
+    x = rng.standard_normal((B, Cin, T)).astype(np.float32)
+    w = (rng.standard_normal((Cout, Cin, k)) / np.sqrt(Cin * k)).astype(np.float32)
+    b = rng.standard_normal(Cout).astype(np.float32)
+    res = rng.standard_normal((B, Cout, T)).astype(np.float32)
+    acc = rng.standard_normal((B, Cout, T)).astype(np.float32)
+    ref = (O.conv1d(x.astype(np.float64), w.astype(np.float64), b, d) + res) / 3.0 + acc
+    xn = _t(np.transpose(x, (0, 2, 1)))
+    kw = dict(residual=_t(np.transpose(res, (0, 2, 1))), accum=_t(np.transpose(acc, (0, 2, 1))), out_scale=1.0 / 3.0)
+    y = ops.conv1d_nlc(ops.split_bf16x3(xn), ops.pack_conv1d_weight(_t(w), 2), _t(b), d, 2, **kw)
+    y0 = ops.conv1d_nlc(xn, ops.pack_conv1d_weight(_t(w), 0), _t(b), d, 0, **kw)
+    yn = np.transpose(y.cpu().numpy(), (0, 2, 1))
+    assert rel_err(ref, yn) < 1e-5
+    assert rel_err(np.transpose(y0.cpu().numpy(), (0, 2, 1)), yn) < 4e-6
+
+
+@pytest.mark.parametrize("case", CONVT_CASES_SPLIT)
+def test_convtranspose1d_split_f32_on_tcgen05(ops, case):
+    B, Cin, Cout, T, K, u = case
+    rng = np.random.default_rng(hash(case) % 2 ** 31 + 2)
+    x = rng.standard_normal((B, Cin, T)).astype(np.float32)
+    w = (rng.standard_normal((Cin, Cout, K)) / np.sqrt(Cin * K / u)).astype(np.float32)
+    b = rng.standard_normal(Cout).astype(np.float32)
+    ref = O.conv_transpose1d(x.astype(np.float64), w.astype(np.float64), b, u, (K - u) // 2)
+    y = ops.convtranspose1d_nlc(ops.split_bf16x3(_t(np.transpose(x, (0, 2, 1)))), ops.pack_convtranspose1d_weight(_t(w), u, 2),
+                                _t(b), K, u, 2)
+    assert tuple(y.shape) == (B, T * u, Cout)
+    assert rel_err(ref, np.transpose(y.cpu().numpy(), (0, 2, 1))) < 1e-5
+
+
+def test_activation1d_nlc_split_output(ops):
+    """Activation1d with the bf16x3 split output == split(fp32 output) bit for bit (both kernels: TMA and direct)."""
+    rng = np.random.default_rng(13)
+    for C, T in ((24, 333), (96, 1000), (10, 40)):
+        x = _t(rng.standard_normal((2, T, C)).astype(np.float32) * 2)
+        al, be = _t(0.5 * rng.standard_normal(C).astype(np.float32)), _t(0.5 * rng.standard_normal(C).astype(np.float32))
+        y32 = ops.activation1d_nlc(x, al, be, torch.float32, True)
+        ys = ops.activation1d_nlc(x, al, be, ops.BF16X3, True)
+        if C % 4 == 0:
+            assert torch.equal(ys, ops.split_bf16x3(y32))
+        else:
+            yd = ys.float().double().cpu().numpy()
+            np.testing.assert_array_equal(yd[..., :C] + yd[..., C:2 * C] + yd[..., 5 * C:], y32.double().cpu().numpy())
+
+
 CONVT_CASES = [(2, 1536, 768, 20, 8, 4), (1, 768, 384, 70, 8, 4), (1, 384, 192, 130, 4, 2), (1, 192, 96, 129, 4, 2),
                (2, 96, 48, 300, 4, 2), (1, 48, 24, 257, 4, 2), (1, 16, 8, 1, 8, 4)]
 
