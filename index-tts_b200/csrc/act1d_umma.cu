@@ -28,9 +28,11 @@
 // Work decomposition: a CTA processes units of 128 signals = (128 / cw time blocks) x (cw channels), cw = the largest
 // power of two <= 128 dividing C, so every C % 8 == 0 fills all 128 lanes.  A lane marches along its time block in
 // chunks of 32 output rows; per chunk c:  stage-in X(c) -> UP(c) -> snake(c) -> V(c) -> DOWN(c-1) -> out(c-1).
-// Warp 0 issues the MMAs; two warpgroups (warps 1-4 and 5-8, each covering the 128 TMEM lanes) alternate chunks, so the
-// snake of chunk c (MUFU-bound: one cosine per 2x sample) overlaps the MMAs and the global loads / stores of its
-// neighbours.  All hand-offs are mbarriers (full/empty per ring slot); MMA completion arrives through tcgen05.commit.
+// Warp 0 issues the up-sampler MMAs and warp 17 the low-pass MMAs (an issuer spends more time on its barrier waits than on
+// its 3 / 5 instructions, so the two chains run in parallel); two groups of eight compute warps alternate chunks, and
+// inside a group two warps per TMEM lane quarter split a chunk's rows / columns in halves, so the snake of chunk c
+// (MUFU-bound: one cosine per 2x sample) overlaps the MMAs and the global loads / stores of its neighbours.  All hand-offs are mbarriers (full/empty per ring slot); MMA completion arrives
+// through tcgen05.commit.
 #include "bvg_common.cuh"
 #include "sm100_ptx.cuh"
 #include "tma_host.cuh"
@@ -41,7 +43,7 @@
 
 namespace bvg {
 
-constexpr int AU_THREADS = 288;        // warp 0: MMA issuer / TMEM owner; warps 1-4: group 0; warps 5-8: group 1
+constexpr int AU_THREADS = 576;        // warp 0: UP issuer / TMEM owner; warps 1-16: compute; warp 17: DOWN issuer
 constexpr int AU_CHUNK = 32;           // output rows per chunk (64 samples of the 2x signal)
 // tensor-memory columns
 constexpr uint32_t AU_DU = 0;          // 2 accumulators x 64 columns: U of a chunk (fp32)
@@ -49,7 +51,7 @@ constexpr uint32_t AU_DY = 128;        // 2 accumulators x 32 columns: Y of a ch
 constexpr uint32_t AU_X = 192;         // ring of 4 chunks x 16 columns (32 fp16 x-rows each) + 8 mirror columns
 constexpr uint32_t AU_V = 272;         // ring of 4 chunks x 32 columns (64 fp16 v-rows each) + 8 mirror columns
 constexpr uint32_t AU_TMEM_COLS = 512;
-constexpr int AU_SMEM_BYTES = 1024 + 8192 + 8192 + 512;
+constexpr int AU_SMEM_BYTES = 1024 + 8192 + 8192 + 256 + 4096 + 64;
 
 struct ActUmmaParams {
     const void* x;
@@ -63,6 +65,8 @@ struct ActUmmaParams {
     uint32_t n_cchunks;      // C / cw
     uint32_t groups_per_b;   // time-block groups per batch item
     uint32_t n_units;
+    int dbg;                 // developer attribution toggles (BVG_ACT_DBG): 1 no cosine, 2 no global loads, 4 no stores,
+                             // 8 one K-step per MMA chain (results are wrong with any of them set)
 };
 
 __device__ __forceinline__ void tmem_st_x16(uint32_t taddr, const uint32_t (&v)[16]) {
@@ -94,6 +98,21 @@ __device__ __forceinline__ void umma_f16_ts(uint32_t d_tmem, uint32_t a_tmem, ui
 // kind::f16 instruction descriptor: D fp32, A fp16, B fp16, both K-major
 __host__ __device__ constexpr uint32_t umma_idesc_f16_f32(uint32_t M, uint32_t N) {
     return (1u << 4) | ((N >> 3) << 17) | ((M >> 4) << 24);
+}
+
+// Wait for up to three barriers at once (whole warp): the try_waits are issued back to back so their latencies overlap
+// instead of adding up (an already-complete try_wait still costs ~90 cycles).
+__device__ __forceinline__ void mbar_wait_warp3(uint64_t* b0, uint32_t p0, uint64_t* b1, uint32_t p1, uint64_t* b2, uint32_t p2) {
+    uint32_t spins = 0;
+    long long t0 = 0;
+    bool d0 = false, d1 = (b1 == nullptr), d2 = false;
+    for (;;) {
+        if (!d0) d0 = mbar_try_wait(b0, p0);
+        if (!d1) d1 = mbar_try_wait(b1, p1);
+        if (!d2) d2 = mbar_try_wait(b2, p2);
+        if (__all_sync(0xffffffffu, d0 && d1 && d2)) return;
+        mbar_backoff(spins, t0);
+    }
 }
 
 // 12-tap filter (bvg_common.cuh): f[k] = F[min(k, 11 - k)]
@@ -148,7 +167,28 @@ __device__ __forceinline__ uint32_t au_pack_half2(float lo, float hi) {
     return *reinterpret_cast<const uint32_t*>(&h);
 }
 
-template <typename TIn, typename TOut>
+template <typename TOut>
+struct AuOut;
+template <>
+struct AuOut<float> {  // two consecutive rows (stride elements apart) of one channel
+    static __device__ __forceinline__ void store2(float* p, int stride, float2 v, bool ok0, bool ok1) {
+        if (ok0) p[0] = v.x;
+        if (ok1) p[stride] = v.y;
+    }
+};
+template <>
+struct AuOut<__nv_bfloat16> {
+    static __device__ __forceinline__ void store2(__nv_bfloat16* p, int stride, float2 v, bool ok0, bool ok1) {
+        const __nv_bfloat162 h = __float22bfloat162_rn(v);
+        if (ok0) p[0] = __low2bfloat16(h);
+        if (ok1) p[stride] = __high2bfloat16(h);
+    }
+};
+
+// CS: channel count (row stride in elements) as a compile-time constant, 0 = runtime.  With a constant stride every row
+// access of a lane is one instruction with an immediate offset; with a runtime stride each costs a 64-bit add on top
+// (ncu r02f: 166 IMAD + 89 IADD3 of 1100 instructions per chunk were address arithmetic).
+template <typename TIn, typename TOut, int CS>
 __global__ void __launch_bounds__(AU_THREADS, 1)
 act1d_umma_kernel(const __grid_constant__ ActUmmaParams p) {
     extern __shared__ uint8_t au_smem_raw[];
@@ -156,15 +196,18 @@ act1d_umma_kernel(const __grid_constant__ ActUmmaParams p) {
     uint8_t* sBup = smem;          // [64 rows = u-time][64 K] fp16: K = 48 used
     uint8_t* sBdn = smem + 8192;   // 2 K-blocks x [32 rows = y-time][64 K] fp16: K = 80 used
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 16384);
-    uint64_t* x_full = bars;          // [4] count 4 (the producing group's warps)
+    uint64_t* x_full = bars;          // [4] count 4 (the IO warps of the staging group)
     uint64_t* x_empty = bars + 4;     // [4] count 1 (tcgen05.commit)
-    uint64_t* v_full = bars + 8;      // [4] count 4
-    uint64_t* v_empty = bars + 12;    // [4] count 1
+    uint64_t* v_full = bars + 8;      // [4] count 4 (the snake warps)
+    uint64_t* v_empty = bars + 12;    // [4] count 1 (tcgen05.commit)
     uint64_t* du_full = bars + 16;    // [2] count 1
     uint64_t* du_empty = bars + 18;   // [2] count 4
     uint64_t* dy_full = bars + 20;    // [2] count 1
     uint64_t* dy_empty = bars + 22;   // [2] count 4
     uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 24);
+    // last valid activated sample per signal (replicate padding of the 2x signal on the right), handed from the snake warp
+    // of one chunk to the snake warp of the next (the other group): [V ring slot][128 signals]
+    float* vl_end = reinterpret_cast<float*>(smem + 16384 + 256);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     griddep_launch_dependents();  // PDL: the prologue below touches constants only
@@ -179,6 +222,7 @@ act1d_umma_kernel(const __grid_constant__ ActUmmaParams p) {
         }
         fence_barrier_init();
     }
+    for (int e = threadIdx.x; e < 4 * 128; e += AU_THREADS) vl_end[e] = 0.f;
     // Toeplitz operands
     for (int e = threadIdx.x; e < 64 * 64; e += AU_THREADS) {
         const int n = e >> 6, k = e & 63;
@@ -200,61 +244,70 @@ act1d_umma_kernel(const __grid_constant__ ActUmmaParams p) {
     uint32_t G0 = 0;  // running chunk number at the start of the unit: identical in every role, drives all ring slots
 
     if (warp == 0) {
-        // ------------------------------ MMA issuer ------------------------------
+        // ------------------------------ UP issuer: U chunk j from X chunk j and the first half of X chunk j + 1 ----------
         const bool leader = elect_one();
-        const uint32_t idesc_up = umma_idesc_f16_f32(128, 64), idesc_dn = umma_idesc_f16_f32(128, 32);
-        const uint64_t bup = umma_desc_sw128_kmajor(smem_u32(sBup)), bdn = umma_desc_sw128_kmajor(smem_u32(sBdn));
-        uint32_t dyc[2] = {0u, 0u};  // uses of each Y accumulator so far
+        const uint32_t idesc_up = umma_idesc_f16_f32(128, 64);
+        const uint64_t bup = umma_desc_sw128_kmajor(smem_u32(sBup));
         for (uint32_t unit = blockIdx.x; unit < p.n_units; unit += gridDim.x) {
-            for (int j = 0; j <= nc + 1; ++j) {
-                if (j <= nc) {  // UP(j): U chunk j from X chunk j and the first half of X chunk j + 1
-                    const uint32_t G = G0 + j, slot = G & 3u, q = G & 1u;
-                    mbar_wait_warp(&x_full[slot], (G >> 2) & 1u);
-                    if (j < nc) mbar_wait_warp(&x_full[(G + 1) & 3u], ((G + 1) >> 2) & 1u);
-                    mbar_wait_warp(&du_empty[q], ((G >> 1) & 1u) ^ 1u);
-                    tc_fence_after_sync();
-                    if (leader) {
-                        const int ksteps = j < nc ? 3 : 2;  // the last chunk of a block needs rows of its own X chunk only
-                        const uint32_t d = tmem_base + AU_DU + 64u * q, a = tmem_base + AU_X + 16u * slot;
-                        for (int kk = 0; kk < ksteps; ++kk) umma_f16_ts(d, a + 8u * kk, bup + 2u * kk, idesc_up, kk > 0);
-                        umma_commit(&du_full[q]);
-                        umma_commit(&x_empty[slot]);
-                    }
-                    __syncwarp();
+            for (int j = 0; j <= nc; ++j) {
+                const uint32_t G = G0 + j, slot = G & 3u, q = G & 1u;
+                mbar_wait_warp3(&x_full[slot], (G >> 2) & 1u, j < nc ? &x_full[(G + 1) & 3u] : nullptr, ((G + 1) >> 2) & 1u,
+                                &du_empty[q], ((G >> 1) & 1u) ^ 1u);
+                tc_fence_after_sync();
+                if (leader) {
+                    const int ksteps = (p.dbg & 8) ? 1 : (j < nc ? 3 : 2);  // the last chunk needs rows of its own X chunk only
+                    const uint32_t d = tmem_base + AU_DU + 64u * q, a = tmem_base + AU_X + 16u * slot;
+                    for (int kk = 0; kk < ksteps; ++kk) umma_f16_ts(d, a + 8u * kk, bup + 2u * kk, idesc_up, kk > 0);
+                    umma_commit(&du_full[q]);
+                    umma_commit(&x_empty[slot]);
                 }
-                const int s = j - 2;
-                if (s >= 0 && s < nc) {  // DOWN(s): Y chunk s from V chunk s and the first 16 samples of V chunk s + 1
-                    const uint32_t G = G0 + s, slot = G & 3u, q = G & 1u;
-                    mbar_wait_warp(&v_full[slot], (G >> 2) & 1u);
-                    mbar_wait_warp(&v_full[(G + 1) & 3u], ((G + 1) >> 2) & 1u);
-                    mbar_wait_warp(&dy_empty[q], (dyc[q] & 1u) ^ 1u);
-                    tc_fence_after_sync();
-                    if (leader) {
-                        const uint32_t d = tmem_base + AU_DY + 32u * q, a = tmem_base + AU_V + 32u * slot;
-                        for (int kk = 0; kk < 5; ++kk)
-                            umma_f16_ts(d, a + 8u * kk, kk < 4 ? bdn + 2u * kk : bdn + (4096u >> 4), idesc_dn, kk > 0);
-                        umma_commit(&dy_full[q]);
-                        umma_commit(&v_empty[slot]);
-                        if (s == nc - 1) umma_commit(&v_empty[(G + 1) & 3u]);  // V chunk nc has no DOWN of its own
-                    }
-                    __syncwarp();
-                    ++dyc[q];
+                __syncwarp();
+            }
+            G0 += static_cast<uint32_t>(nc) + 1u;
+        }
+    } else if (warp == AU_THREADS / 32 - 1) {
+        // ------------------------------ DOWN issuer: Y chunk s from V chunk s and the first 16 samples of V chunk s + 1 ---
+        const bool leader = elect_one();
+        const uint32_t idesc_dn = umma_idesc_f16_f32(128, 32);
+        const uint64_t bdn = umma_desc_sw128_kmajor(smem_u32(sBdn));
+        uint32_t dyc0 = 0u, dyc1 = 0u;  // uses of each Y accumulator so far
+        for (uint32_t unit = blockIdx.x; unit < p.n_units; unit += gridDim.x) {
+            for (int s = 0; s < nc; ++s) {
+                const uint32_t G = G0 + s, slot = G & 3u, q = G & 1u;
+                const uint32_t use = q ? dyc1 : dyc0;
+                mbar_wait_warp3(&v_full[slot], (G >> 2) & 1u, &v_full[(G + 1) & 3u], ((G + 1) >> 2) & 1u, &dy_empty[q],
+                                (use & 1u) ^ 1u);
+                tc_fence_after_sync();
+                if (leader) {
+                    const uint32_t d = tmem_base + AU_DY + 32u * q, a = tmem_base + AU_V + 32u * slot;
+                    for (int kk = 0; kk < ((p.dbg & 8) ? 1 : 5); ++kk)
+                        umma_f16_ts(d, a + 8u * kk, kk < 4 ? bdn + 2u * kk : bdn + (4096u >> 4), idesc_dn, kk > 0);
+                    umma_commit(&dy_full[q]);
+                    umma_commit(&v_empty[slot]);
+                    if (s == nc - 1) umma_commit(&v_empty[(G + 1) & 3u]);  // V chunk nc has no DOWN of its own
                 }
+                __syncwarp();
+                if (q) ++dyc1; else ++dyc0;
             }
             G0 += static_cast<uint32_t>(nc) + 1u;
         }
     } else {
-        // ------------------------------ compute groups ------------------------------
-        const uint32_t wg = static_cast<uint32_t>(warp - 1) >> 2;       // 0 / 1: owns the chunks with G % 2 == wg
-        const uint32_t quarter = static_cast<uint32_t>(warp) & 3u;      // TMEM lane quarter this warp may access
-        const uint32_t sig = quarter * 32u + static_cast<uint32_t>(lane);  // signal (TMEM lane) of this thread
+        // ------------------------------ compute warps ------------------------------
+        // 16 warps = 2 groups (chunk parity) x 2 roles x 4 TMEM lane quarters.  Role 0 ("IO") loads a chunk's x rows, stages
+        // them into the X ring and writes the output rows; role 1 ("snake") turns U into V.  Four warps per scheduler in
+        // different phases (global loads, MUFU-bound snake, stores) keep the issue slots busy.
+        const uint32_t widx = static_cast<uint32_t>(warp - 1);
+        const uint32_t wg = widx >> 3;                                   // owns the chunks with G % 2 == wg
+        const uint32_t role = (widx >> 2) & 1u;
+        const uint32_t quarter = static_cast<uint32_t>(warp) & 3u;       // TMEM lane quarter this warp may access
+        const uint32_t sig = quarter * 32u + static_cast<uint32_t>(lane);   // signal (TMEM lane) of this thread
         const uint32_t tl = tmem_base + ((quarter * 32u) << 16);
         const int cw_mask = (1 << p.cw_shift) - 1;
-        const int64_t T = p.T, C = p.C;
-        const int64_t Lq = static_cast<int64_t>(nc) * AU_CHUNK;
-        const int64_t ntb = 128 >> p.cw_shift;
+        const int T = static_cast<int>(p.T);          // the launcher guarantees T * C * 4 < 2^31: 32-bit row arithmetic
+        const int Ci = CS > 0 ? CS : p.C;
+        const int Lq = nc * AU_CHUNK;
+        const int ntb = 128 >> p.cw_shift;
         uint32_t dyc = 0;     // uses of this group's Y accumulator
-        float vl = 0.f;       // last valid activated sample (replicate padding of the 2x signal on the right)
 
         for (uint32_t unit = blockIdx.x; unit < p.n_units; unit += gridDim.x) {
             const uint32_t cc = unit % p.n_cchunks;
@@ -262,129 +315,178 @@ act1d_umma_kernel(const __grid_constant__ ActUmmaParams p) {
             const uint32_t b = rest / p.groups_per_b;
             const uint32_t g = rest - b * p.groups_per_b;
             const int ch = static_cast<int>(cc << p.cw_shift) + (static_cast<int>(sig) & cw_mask);
-            const int64_t y0 = (static_cast<int64_t>(g) * ntb + (sig >> p.cw_shift)) * Lq;  // first output row of this lane
-            const float a2 = 2.0f * expf(__ldg(p.alpha + ch));
-            const float cb = 0.5f / (expf(__ldg(p.beta + ch)) + 1e-9f);
-            const TIn* xb = static_cast<const TIn*>(p.x) + static_cast<int64_t>(b) * T * C + ch;
-            TOut* yb = static_cast<TOut*>(p.y) + static_cast<int64_t>(b) * T * C + ch;
-            const float2 a2v = make_float2(a2, a2), ncb = make_float2(-cb, -cb);
+            // first output row of this lane; lanes whose block starts past the end are parked on the last block's rows
+            // (their loads stay in bounds, their stores are masked)
+            const int64_t y0l = (static_cast<int64_t>(g) * ntb + (sig >> p.cw_shift)) * Lq;
+            const bool lane_live = y0l < T;
+            const int y0 = lane_live ? static_cast<int>(y0l) : 0;
+            const int i0 = ((G0 & 1u) == wg) ? 0 : 1;
 
-            float xr[32];  // prefetched x rows of the next chunk this group stages (as fp32)
-            auto load_chunk = [&](int i) {
-                const int64_t t0 = y0 - 8 + static_cast<int64_t>(i) * AU_CHUNK;
-                const bool interior = (t0 >= 0) && (t0 + 31 < T);
-                if (__all_sync(0xffffffffu, interior)) {
-                    const TIn* pr = xb + t0 * C;
+            if (role == 0u) {
+                // ================= IO warp: stage-in X chunk i, prefetch chunk i + 2, write Y chunk i - 4 =================
+                const float cb = 0.5f / (expf(__ldg(p.beta + ch)) + 1e-9f);
+                const float2 pcb = make_float2(cb, cb);
+                const TIn* xb = static_cast<const TIn*>(p.x) + static_cast<int64_t>(b) * T * Ci + ch;
+                TOut* yb = static_cast<TOut*>(p.y) + static_cast<int64_t>(b) * T * Ci + ch;
+                float xr[32];  // prefetched x rows of the next chunk this warp stages (as fp32)
+                auto load_chunk = [&](int i) {
+                    const int t0 = y0 - 8 + i * AU_CHUNK;
+                    const bool interior = (t0 >= 0) && (t0 + 31 < T);
+                    if (p.dbg & 2) {
 #pragma unroll
-                    for (int r = 0; r < 32; ++r) xr[r] = AuIO<TIn>::load(pr + r * C);
-                } else {  // replicate padding of x at the sequence ends (and finite data for lanes past the end)
+                        for (int r = 0; r < 32; ++r) xr[r] = static_cast<float>(r + lane) * 0.01f;
+                    } else if (__all_sync(0xffffffffu, interior)) {
+                        const TIn* pr = xb + static_cast<int64_t>(t0) * Ci;
 #pragma unroll
-                    for (int r = 0; r < 32; ++r) {
-                        int64_t t = t0 + r;
-                        t = t < 0 ? 0 : (t >= T ? T - 1 : t);
-                        xr[r] = AuIO<TIn>::load(xb + t * C);
+                        for (int r = 0; r < 32; ++r) xr[r] = AuIO<TIn>::load(pr + r * Ci);
+                    } else {  // replicate padding of x at the sequence ends (and in-bounds data for rows past the end)
+#pragma unroll
+                        for (int r = 0; r < 32; ++r) {
+                            int t = t0 + r;
+                            t = t < 0 ? 0 : (t >= T ? T - 1 : t);
+                            xr[r] = AuIO<TIn>::load(xb + static_cast<int64_t>(t) * Ci);
+                        }
+                    }
+                };
+                // The register prefetch keeps one chunk (4 KB per warp, 32 KB per SM) in flight -- at ~1.2 us of loaded DRAM
+                // latency that is 4 TB/s for the whole chip (measured: exactly that).  An L2 prefetch of the chunk after
+                // next costs one instruction per row and no registers, and turns the later loads into L2 hits.
+                auto prefetch_chunk = [&](int i) {
+                    const int t0 = y0 - 8 + i * AU_CHUNK;
+                    const bool interior = (t0 >= 0) && (t0 + 31 < T);
+                    if (!(p.dbg & 2) && __all_sync(0xffffffffu, interior)) {
+                        const TIn* pr = xb + static_cast<int64_t>(t0) * Ci;
+#pragma unroll
+                        for (int r = 0; r < 32; ++r) asm volatile("prefetch.global.L2 [%0];" ::"l"(pr + r * Ci));
+                    }
+                };
+                if (i0 <= nc) load_chunk(i0);
+                if (i0 + 2 <= nc) prefetch_chunk(i0 + 2);
+                for (int i = i0; i <= nc + 4; i += 2) {
+                    const uint32_t G = G0 + static_cast<uint32_t>(i);
+                    if (i + 4 <= nc) prefetch_chunk(i + 4);
+                    if (i <= nc) {
+                        const uint32_t slot = G & 3u;
+                        uint32_t pk[16];
+#pragma unroll
+                        for (int r = 0; r < 16; ++r) pk[r] = au_pack_half2(xr[2 * r], xr[2 * r + 1]);
+                        mbar_wait_warp(&x_empty[slot], ((G >> 2) & 1u) ^ 1u);
+                        tc_fence_after_sync();
+                        tmem_st_x16(tl + AU_X + 16u * slot, pk);
+                        if (slot == 0u) tmem_st_x8(tl + AU_X + 64u, pk);  // mirror: a slot-3 window runs on into it
+                        tmem_st_wait();
+                        tc_fence_before_sync();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(&x_full[slot]);
+                    }
+                    if (i + 2 <= nc) load_chunk(i + 2);
+                    const int s = i - 4;
+                    if (s >= 0 && s < nc) {
+                        // ---- out: Y chunk s (fp32, 32 columns) + c -> rows y0 + 32 s .. of this lane's channel
+                        mbar_wait_warp(&dy_full[wg], dyc & 1u);
+                        tc_fence_after_sync();
+                        uint32_t dv[32];
+                        tmem_ld_32x32b_x32(tl + AU_DY + 32u * wg, dv);
+                        tmem_ld_wait();
+                        tc_fence_before_sync();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(&dy_empty[wg]);
+                        ++dyc;
+                        const int t0 = y0 + s * AU_CHUNK;
+                        const int left_rows = lane_live ? T - t0 : 0;
+                        const int n_ok = (p.dbg & 4) ? 0 : (left_rows >= 32 ? 32 : (left_rows < 0 ? 0 : left_rows));
+                        TOut* pr = yb + static_cast<int64_t>(t0) * Ci;
+                        if (__all_sync(0xffffffffu, n_ok == 32)) {
+#pragma unroll
+                            for (int r = 0; r < 32; r += 2) {
+                                const float2 o = __fadd2_rn(make_float2(__uint_as_float(dv[r]), __uint_as_float(dv[r + 1])), pcb);
+                                AuOut<TOut>::store2(pr + r * Ci, Ci, o, true, true);
+                            }
+                        } else {
+#pragma unroll
+                            for (int r = 0; r < 32; r += 2) {
+                                const float2 o = __fadd2_rn(make_float2(__uint_as_float(dv[r]), __uint_as_float(dv[r + 1])), pcb);
+                                AuOut<TOut>::store2(pr + r * Ci, Ci, o, r < n_ok, r + 1 < n_ok);
+                            }
+                        }
                     }
                 }
-            };
-
-            const int i0 = ((G0 & 1u) == wg) ? 0 : 1;
-            if (i0 <= nc) load_chunk(i0);
-            for (int i = i0; i <= nc + 4; i += 2) {
-                const uint32_t G = G0 + static_cast<uint32_t>(i);
-                if (i <= nc) {
-                    // ---- stage-in: X chunk i (32 rows) -> fp16 pairs -> 16 TMEM columns of ring slot G % 4
-                    const uint32_t slot = G & 3u;
-                    uint32_t pk[16];
-#pragma unroll
-                    for (int r = 0; r < 16; ++r) pk[r] = au_pack_half2(xr[2 * r], xr[2 * r + 1]);
-                    mbar_wait_warp(&x_empty[slot], ((G >> 2) & 1u) ^ 1u);
-                    tc_fence_after_sync();
-                    tmem_st_x16(tl + AU_X + 16u * slot, pk);
-                    if (slot == 0u) tmem_st_x8(tl + AU_X + 64u, pk);  // mirror: the window of a slot-3 chunk runs on into it
-                    tmem_st_wait();
-                    tc_fence_before_sync();
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(&x_full[slot]);
-                }
-                if (i + 2 <= nc) load_chunk(i + 2);
-                const int j = i - 2;
-                if (j >= 0 && j <= nc) {
-                    // ---- snake: U chunk j (fp32, 64 columns) -> v = u - c cos(2 a u) -> fp16 -> V ring slot
-                    const uint32_t Gj = G - 2u, slot = Gj & 3u;
+            } else {
+                // ================= snake warp: U chunk j (fp32, 64 columns) -> v = u - c cos(2 a u) -> fp16 -> V ring slot ===
+                const float a2 = 2.0f * expf(__ldg(p.alpha + ch));
+                const float cb = 0.5f / (expf(__ldg(p.beta + ch)) + 1e-9f);
+                const float2 a2v = make_float2(a2, a2), ncb = make_float2(-cb, -cb);
+                for (int j = i0; j <= nc; j += 2) {
+                    const uint32_t Gj = G0 + static_cast<uint32_t>(j), slot = Gj & 3u;
                     mbar_wait_warp(&du_full[wg], (Gj >> 1) & 1u);
-                    mbar_wait_warp(&v_empty[slot], ((Gj >> 2) & 1u) ^ 1u);
                     tc_fence_after_sync();
                     // column q of the chunk is 2x-sample 2*y0 + 64*j - 8 + q of this lane's sequence
-                    const int64_t n0 = 2 * y0 + 64 * static_cast<int64_t>(j) - 8;
-                    const bool left = (y0 == 0) && (j == 0);
-                    const int64_t ql64 = 2 * T - 1 - n0;
-                    const int qlast = ql64 > 64 ? 64 : (ql64 < -1 ? -1 : static_cast<int>(ql64));  // column of sample 2T-1
-                    const bool edge = __any_sync(0xffffffffu, left || qlast < 63);
+                    const int n0 = 2 * y0 + 64 * j - 8;
+                    const bool left = lane_live && (y0 == 0) && (j == 0);
+                    const int qd = 2 * T - 1 - n0;
+                    const int qlast = !lane_live ? 64 : (qd > 64 ? 64 : (qd < -1 ? -1 : qd));  // column of sample 2T-1
+                    const bool edge = __any_sync(0xffffffffu, left || qlast <= 63);
+                    float vl = 0.f;
+                    if (edge && j > 0) {
+                        // Replicate padding on the right: samples after 2T-1 repeat v[2T-1], which the previous chunk's
+                        // snake warp (other group) may have produced: it travels through shared memory, ordered by that
+                        // chunk's v_full barrier.
+                        mbar_wait_warp(&v_full[(Gj - 1u) & 3u], ((Gj - 1u) >> 2) & 1u);
+                        vl = vl_end[((Gj - 1u) & 3u) * 128u + sig];
+                    }
+                    mbar_wait_warp(&v_empty[slot], ((Gj >> 2) & 1u) ^ 1u);
+                    tc_fence_after_sync();
+                    // 32 columns at a time; each pair is activated and packed at once (registers: 96 per thread with 18
+                    // warps -- five warps share one scheduler's register file)
 #pragma unroll
                     for (int h = 0; h < 2; ++h) {
                         uint32_t uv[32];
                         tmem_ld_32x32b_x32(tl + AU_DU + 64u * wg + 32u * h, uv);
                         tmem_ld_wait();
-                        if (h == 1) {  // both halves are in registers: hand the accumulator back to the MMA warp
+                        if (h == 1) {  // U is in registers: hand the accumulator back to the UP issuer
                             tc_fence_before_sync();
                             __syncwarp();
                             if (lane == 0) mbar_arrive(&du_empty[wg]);
                         }
-                        float v[32];
-#pragma unroll
-                        for (int e = 0; e < 32; e += 2) {
-                            const float2 u = make_float2(__uint_as_float(uv[e]), __uint_as_float(uv[e + 1]));
-                            const float2 t = __fmul2_rn(u, a2v);
-                            const float2 cs = make_float2(__cosf(t.x), __cosf(t.y));
-                            const float2 r = __ffma2_rn(ncb, cs, u);
-                            v[e] = r.x;
-                            v[e + 1] = r.y;
-                        }
-                        if (edge) {
-                            if (left && h == 0) {  // samples before 0 repeat v[0] (column 8 of the first chunk)
-#pragma unroll
-                                for (int e = 0; e < 8; ++e) v[e] = v[8];
-                            }
-#pragma unroll
-                            for (int e = 0; e < 32; ++e) {  // samples after 2T-1 repeat v[2T-1]
-                                if (32 * h + e > qlast) v[e] = vl; else vl = v[e];
-                            }
-                        }
                         uint32_t pk[16];
+                        if (p.dbg & 1) {
 #pragma unroll
-                        for (int e = 0; e < 16; ++e) pk[e] = au_pack_half2(v[2 * e], v[2 * e + 1]);
+                            for (int e = 0; e < 32; e += 2) pk[e >> 1] = au_pack_half2(__uint_as_float(uv[e]), __uint_as_float(uv[e + 1]));
+                        } else if (!edge) {
+#pragma unroll
+                            for (int e = 0; e < 32; e += 2) {
+                                const float2 u = make_float2(__uint_as_float(uv[e]), __uint_as_float(uv[e + 1]));
+                                const float2 t = __fmul2_rn(u, a2v);
+                                const float2 cs = make_float2(__cosf(t.x), __cosf(t.y));
+                                const float2 r = __ffma2_rn(ncb, cs, u);
+                                pk[e >> 1] = au_pack_half2(r.x, r.y);
+                            }
+                        } else {
+                            float v0 = 0.f;  // v[0] of the sequence = column 8 of the first chunk (left replicate padding)
+                            if (left && h == 0) {
+                                const float u8 = __uint_as_float(uv[8]);
+                                v0 = fmaf(-cb, __cosf(u8 * a2), u8);
+                            }
+#pragma unroll
+                            for (int e = 0; e < 32; e += 2) {
+                                const float2 u = make_float2(__uint_as_float(uv[e]), __uint_as_float(uv[e + 1]));
+                                const float2 t = __fmul2_rn(u, a2v);
+                                const float2 cs = make_float2(__cosf(t.x), __cosf(t.y));
+                                float2 r = __ffma2_rn(ncb, cs, u);
+                                if (left && h == 0 && e < 8) r = make_float2(v0, v0);
+                                if (32 * h + e > qlast) r.x = vl; else vl = r.x;      // samples after 2T-1 repeat v[2T-1]
+                                if (32 * h + e + 1 > qlast) r.y = vl; else vl = r.y;
+                                pk[e >> 1] = au_pack_half2(r.x, r.y);
+                            }
+                        }
                         tmem_st_x16(tl + AU_V + 32u * slot + 16u * h, pk);
                         if (h == 0 && slot == 0u) tmem_st_x8(tl + AU_V + 128u, pk);  // mirror (see X ring)
                     }
+                    if (edge) vl_end[slot * 128u + sig] = vl;
                     tmem_st_wait();
                     tc_fence_before_sync();
                     __syncwarp();
                     if (lane == 0) mbar_arrive(&v_full[slot]);
-                }
-                const int s = i - 4;
-                if (s >= 0 && s < nc) {
-                    // ---- out: Y chunk s (fp32, 32 columns) + c -> rows y0 + 32 s .. of this lane's channel
-                    mbar_wait_warp(&dy_full[wg], dyc & 1u);
-                    tc_fence_after_sync();
-                    uint32_t dv[32];
-                    tmem_ld_32x32b_x32(tl + AU_DY + 32u * wg, dv);
-                    tmem_ld_wait();
-                    tc_fence_before_sync();
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(&dy_empty[wg]);
-                    ++dyc;
-                    const int64_t t0 = y0 + static_cast<int64_t>(s) * AU_CHUNK;
-                    const int64_t left_rows = T - t0;
-                    const int n_ok = left_rows >= 32 ? 32 : (left_rows < 0 ? 0 : static_cast<int>(left_rows));
-                    TOut* pr = yb + t0 * C;
-                    if (__all_sync(0xffffffffu, n_ok == 32)) {
-#pragma unroll
-                        for (int r = 0; r < 32; ++r) AuIO<TOut>::store(pr + r * C, __uint_as_float(dv[r]) + cb);
-                    } else {
-#pragma unroll
-                        for (int r = 0; r < 32; ++r)
-                            if (r < n_ok) AuIO<TOut>::store(pr + r * C, __uint_as_float(dv[r]) + cb);
-                    }
                 }
             }
             G0 += static_cast<uint32_t>(nc) + 1u;
@@ -402,25 +504,47 @@ act1d_umma_kernel(const __grid_constant__ ActUmmaParams p) {
 // ------------------------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------------------------
-template <typename TIn, typename TOut>
+template <typename TIn, typename TOut, int CS>
 static int act_umma_attrs() {
     static std::atomic<bool> done[64];
     int dev = 0;
     BVG_CUDA(cudaGetDevice(&dev));
     if (dev >= 0 && dev < 64 && done[dev].load(std::memory_order_acquire)) return BVG_OK;
-    BVG_CUDA(cudaFuncSetAttribute(act1d_umma_kernel<TIn, TOut>, cudaFuncAttributeMaxDynamicSharedMemorySize, AU_SMEM_BYTES));
+    BVG_CUDA(cudaFuncSetAttribute(act1d_umma_kernel<TIn, TOut, CS>, cudaFuncAttributeMaxDynamicSharedMemorySize, AU_SMEM_BYTES));
     if (dev >= 0 && dev < 64) done[dev].store(true, std::memory_order_release);
     return BVG_OK;
 }
 
+template <typename TIn, typename TOut, int CS>
+static int launch_act_umma_cs(const ActUmmaParams& p, int grid, cudaStream_t st) {
+    const int rc = act_umma_attrs<TIn, TOut, CS>();
+    if (rc != BVG_OK) return rc;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(static_cast<unsigned>(grid));
+    cfg.blockDim = dim3(AU_THREADS);
+    cfg.dynamicSmemBytes = AU_SMEM_BYTES;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    BVG_CUDA(cudaLaunchKernelEx(&cfg, act1d_umma_kernel<TIn, TOut, CS>, p));
+    BVG_LAUNCH_CHECK("act1d_umma_kernel");
+    return BVG_OK;
+}
+
 // Returns BVG_OK after launching, a positive value when the shape does not suit this kernel (the caller then uses the
-// SIMT kernel), a negative status on error.
-template <typename TIn, typename TOut>
+// SIMT kernel), a negative status on error.  WIDTHS: the generator's stage widths get a compile-time row stride.
+template <typename TIn, typename TOut, bool WIDTHS>
 static int launch_act_umma(const void* x, void* y, const float* alpha, const float* beta, int64_t B, int64_t T, int64_t C,
                            cudaStream_t st) {
-    if (C % 8 != 0 || C > (1 << 20) || T < 1 || T >= (int64_t(1) << 40)) return 1;
+    // 32-bit row arithmetic inside the kernel
+    if (C % 8 != 0 || C > (1 << 16) || T < 1 || T >= (int64_t(1) << 28) || T * C >= (int64_t(1) << 29)) return 1;
     ActUmmaParams p{};
     p.x = x; p.y = y; p.alpha = alpha; p.beta = beta; p.T = T; p.C = static_cast<int>(C);
+    static const int dbg_env = []() { const char* e = getenv("BVG_ACT_DBG"); return e ? atoi(e) : 0; }();
+    p.dbg = dbg_env;
     int sh = 3;
     while (sh < 7 && C % (int64_t(2) << sh) == 0) ++sh;  // cw = largest power of two <= 128 dividing C
     p.cw_shift = sh;
@@ -446,23 +570,19 @@ static int launch_act_umma(const void* x, void* y, const float* alpha, const flo
     if (units >= (int64_t(1) << 31) || groups >= (int64_t(1) << 31)) return 1;
     p.groups_per_b = static_cast<uint32_t>(groups);
     p.n_units = static_cast<uint32_t>(units);
-    {
-        const int rc = act_umma_attrs<TIn, TOut>();
-        if (rc != BVG_OK) return rc;
+    const int grid = static_cast<int>(units < sms ? units : sms);
+    if (WIDTHS) {
+        switch (C) {
+            case 24: return launch_act_umma_cs<TIn, TOut, 24>(p, grid, st);
+            case 48: return launch_act_umma_cs<TIn, TOut, 48>(p, grid, st);
+            case 96: return launch_act_umma_cs<TIn, TOut, 96>(p, grid, st);
+            case 192: return launch_act_umma_cs<TIn, TOut, 192>(p, grid, st);
+            case 384: return launch_act_umma_cs<TIn, TOut, 384>(p, grid, st);
+            case 768: return launch_act_umma_cs<TIn, TOut, 768>(p, grid, st);
+            default: break;
+        }
     }
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(static_cast<unsigned>(units < sms ? units : sms));
-    cfg.blockDim = dim3(AU_THREADS);
-    cfg.dynamicSmemBytes = AU_SMEM_BYTES;
-    cfg.stream = st;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = pdl_enabled() ? 1 : 0;
-    BVG_CUDA(cudaLaunchKernelEx(&cfg, act1d_umma_kernel<TIn, TOut>, p));
-    BVG_LAUNCH_CHECK("act1d_umma_kernel");
-    return BVG_OK;
+    return launch_act_umma_cs<TIn, TOut, 0>(p, grid, st);
 }
 
 // BVG_ACT_UMMA=0 keeps the SIMT kernel (A/B runs)
@@ -476,17 +596,31 @@ bool act_umma_requested() {
 
 int activation1d_nlc_umma(const void* x, int x_dtype, void* y, int y_dtype, const float* alpha, const float* beta, int64_t B,
                           int64_t T, int64_t C, cudaStream_t st) {
-    if (x_dtype == BVG_F32 && y_dtype == BVG_BF16) return launch_act_umma<float, __nv_bfloat16>(x, y, alpha, beta, B, T, C, st);
+    if (x_dtype == BVG_F32 && y_dtype == BVG_BF16)
+        return launch_act_umma<float, __nv_bfloat16, true>(x, y, alpha, beta, B, T, C, st);
     if (x_dtype == BVG_BF16 && y_dtype == BVG_BF16)
-        return launch_act_umma<__nv_bfloat16, __nv_bfloat16>(x, y, alpha, beta, B, T, C, st);
-    if (x_dtype == BVG_F32 && y_dtype == BVG_F32) return launch_act_umma<float, float>(x, y, alpha, beta, B, T, C, st);
+        return launch_act_umma<__nv_bfloat16, __nv_bfloat16, true>(x, y, alpha, beta, B, T, C, st);
+    if (x_dtype == BVG_F32 && y_dtype == BVG_F32)  // activation_post only: one width, runtime stride
+        return launch_act_umma<float, float, false>(x, y, alpha, beta, B, T, C, st);
     return 1;
 }
 
+template <typename TIn, typename TOut>
+static int act_umma_attrs_widths() {
+    int rc = act_umma_attrs<TIn, TOut, 0>();
+    if (rc == BVG_OK) rc = act_umma_attrs<TIn, TOut, 24>();
+    if (rc == BVG_OK) rc = act_umma_attrs<TIn, TOut, 48>();
+    if (rc == BVG_OK) rc = act_umma_attrs<TIn, TOut, 96>();
+    if (rc == BVG_OK) rc = act_umma_attrs<TIn, TOut, 192>();
+    if (rc == BVG_OK) rc = act_umma_attrs<TIn, TOut, 384>();
+    if (rc == BVG_OK) rc = act_umma_attrs<TIn, TOut, 768>();
+    return rc;
+}
+
 int activation1d_umma_init() {
-    int rc = act_umma_attrs<float, __nv_bfloat16>();
-    if (rc == BVG_OK) rc = act_umma_attrs<__nv_bfloat16, __nv_bfloat16>();
-    if (rc == BVG_OK) rc = act_umma_attrs<float, float>();
+    int rc = act_umma_attrs_widths<float, __nv_bfloat16>();
+    if (rc == BVG_OK) rc = act_umma_attrs_widths<__nv_bfloat16, __nv_bfloat16>();
+    if (rc == BVG_OK) rc = act_umma_attrs<float, float, 0>();
     return rc;
 }
 

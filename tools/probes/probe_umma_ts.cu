@@ -59,6 +59,7 @@ __host__ __device__ constexpr uint32_t idesc_f16_f32(uint32_t M, uint32_t N) {
 // a: [128][KDIM] fp16 row-major; b: [MAXN][KDIM] fp16 row-major (row n = output column n).
 // mode 0: correctness (out[128][MAXN] = A * B^T, A read from TMEM columns A_BASE_COL + acol ...)
 // mode 1: timing of `reps` back-to-back TS MMAs, cycles written to cyc[0]
+// mode 2: fp16 ACCUMULATOR (idesc c_format = 0): raw TMEM columns [0, 64) of every lane are written to out (as bit patterns)
 __global__ void __launch_bounds__(128, 1)
 probe_kernel(const __half* a, const __half* b, float* out, long long* cyc, int N, int acol, int mode, int reps) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -101,8 +102,8 @@ probe_kernel(const __half* a, const __half* b, float* out, long long* cyc, int N
     tc_fence_after_sync();
 
     if (threadIdx.x == 0) {
-        const uint32_t idesc = idesc_f16_f32(128, N);
-        if (mode == 0) {
+        const uint32_t idesc = mode == 2 ? (idesc_f16_f32(128, N) & ~(3u << 4)) : idesc_f16_f32(128, N);
+        if (mode == 0 || mode == 2) {
             for (int ks = 0; ks < KDIM / 16; ++ks) {
                 const uint64_t db = umma_desc_sw128_kmajor(smem_u32(sB) + ks * 32, 0);
                 umma_f16_ts(tmem_base, tmem_base + A_BASE_COL + acol + 8 * ks, db, idesc, ks > 0);
@@ -123,6 +124,14 @@ probe_kernel(const __half* a, const __half* b, float* out, long long* cyc, int N
     __syncwarp();
     mbar_wait(&bars[0], 0);
     tc_fence_after_sync();
+    if (mode == 2) {
+        uint32_t v[32];
+        for (int c = 0; c < 64; c += 32) {
+            tmem_ld_32x32b_x32(tmem_base + ((warp * 32u) << 16) + c, v);
+            tmem_ld_wait();
+            for (int j = 0; j < 32; ++j) out[(warp * 32 + lane) * MAXN + c + j] = __uint_as_float(v[j]);
+        }
+    }
     if (mode == 0) {
         uint32_t v[32];
         for (int c = 0; c < N; c += 32) {
@@ -177,6 +186,31 @@ int main() {
                    bad ? "MISMATCH" : "ok", bad, hout[0], hout[1], hout[2], hout[3]);
         }
     printf("SUMMARY TS-mode A operand: %d/%d ok\n", ok, total);
+
+    // ---- fp16 accumulator: where do the N results of a row live?
+    for (int N : {32, 64}) {
+        CK(cudaMemset(dout, 0, hout.size() * 4));
+        probe_kernel<<<1, 128, smem_bytes>>>(da, db, dout, dcyc, N, 0, 2, 0);
+        CK(cudaGetLastError());
+        cudaError_t e = cudaDeviceSynchronize();
+        if (e != cudaSuccess) { printf("fp16 accumulator: N=%d LAUNCH ERROR %s\n", N, cudaGetErrorString(e)); return 3; }
+        CK(cudaMemcpy(hout.data(), dout, hout.size() * 4, cudaMemcpyDeviceToHost));
+        int bad_packed = 0, bad_low = 0;
+        for (int m = 0; m < 128; ++m)
+            for (int n = 0; n < N; ++n) {
+                float ex = 0.f;
+                for (int k = 0; k < KDIM; ++k) ex += fa[m * KDIM + k] * fb[n * KDIM + k];
+                const uint32_t* raw = reinterpret_cast<const uint32_t*>(&hout[m * MAXN]);
+                const uint32_t wp = raw[n >> 1];
+                const __half hp = __ushort_as_half((unsigned short)((n & 1) ? (wp >> 16) : (wp & 0xffff)));
+                const __half hl = __ushort_as_half((unsigned short)(raw[n] & 0xffff));
+                if (__half2float(hp) != ex) ++bad_packed;
+                if (__half2float(hl) != ex) ++bad_low;
+            }
+        const uint32_t* r0 = reinterpret_cast<const uint32_t*>(&hout[0]);
+        printf("fp16 accumulator N=%d: packed-pairs hypothesis %d mismatches, low-half hypothesis %d mismatches; lane 0 raw: %08x %08x %08x %08x\n",
+               N, bad_packed, bad_low, r0[0], r0[1], r0[2], r0[3]);
+    }
 
     for (int N : {16, 32, 64, 128}) {
         const int reps = 512;
