@@ -33,7 +33,7 @@ namespace bvg {
 // act1d_umma.cu: both FIRs on the tensor cores (fast-sin mode only); positive return = shape not taken
 int activation1d_nlc_umma(const void* x, int x_dtype, void* y, int y_dtype, const float* alpha, const float* beta, int64_t B,
                           int64_t T, int64_t C, cudaStream_t st);
-bool act_umma_requested();
+bool act_umma_requested(int64_t C);
 int activation1d_umma_init();
 
 __device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) { return __ffma2_rn(a, b, c); }
@@ -925,7 +925,7 @@ int activation1d_nlc(const void* x, int x_dtype, void* y, int y_dtype, const flo
     BVG_REQUIRE(C % 2 == 0, BVG_ERR_UNSUPPORTED, "activation1d_nlc: C=%lld must be even", (long long)C);
     BVG_REQUIRE(B <= 65535, BVG_ERR_UNSUPPORTED, "activation1d_nlc: B=%lld > 65535", (long long)B);
     if (B == 0 || T == 0) return BVG_OK;
-    if (!precise && act_umma_requested()) {  // throughput mode: the tensor-core kernel (act1d_umma.cu)
+    if (!precise && act_umma_requested(C)) {  // throughput mode: the tensor-core kernel (act1d_umma.cu)
         const int rc = activation1d_nlc_umma(x, x_dtype, y, y_dtype, alpha, beta, B, T, C, st);
         if (rc <= 0) return rc;
     }
@@ -978,7 +978,7 @@ int activation1d_nlc_multi(const void* x, int x_dtype, void* const* ys, int y_dt
     int h0 = 0;
     // fast-sin mode on shapes the tensor-core kernel takes: one launch per head (three of those beat the shared-up-sampler
     // SIMT kernel, and results stay bit-identical to single calls by construction)
-    const bool per_head = !precise && act_umma_requested() && C % 8 == 0;
+    const bool per_head = !precise && act_umma_requested(C) && C % 8 == 0;
     for (; !per_head && h0 + 3 <= n_heads; h0 += 3) {
         int rc;
         if (x_dtype == BVG_F32 && y_dtype == BVG_BF16)

@@ -585,13 +585,22 @@ static int launch_act_umma(const void* x, void* y, const float* alpha, const flo
     return launch_act_umma_cs<TIn, TOut, 0>(p, grid, st);
 }
 
-// BVG_ACT_UMMA=0 keeps the SIMT kernel (A/B runs)
-bool act_umma_requested() {
-    static const bool v = []() {
+// BVG_ACT_UMMA: "0" keeps the SIMT kernel everywhere, "1" takes every shape the tensor-core kernel supports (A/B runs);
+// unset = automatic: rows of at least AU_AUTO_MIN_C channels.  Narrow rows (C = 24 / 48: 48- and 96-byte rows) make the
+// per-lane global accesses of this kernel scalar and strided, and it loses to the SIMT kernel there (r02: 186 vs 129 us
+// at C = 24); from C = 96 up it is level or ahead (115 vs 129 us at C = 384, f32 -> bf16).
+constexpr int64_t AU_AUTO_MIN_C = 96;
+static int act_umma_mode() {
+    static const int v = []() {
         const char* e = getenv("BVG_ACT_UMMA");
-        return !(e != nullptr && e[0] == '0');
+        if (e == nullptr || e[0] == '\0') return 2;
+        return e[0] == '0' ? 0 : 1;
     }();
     return v;
+}
+bool act_umma_requested(int64_t C) {
+    const int m = act_umma_mode();
+    return m == 1 || (m == 2 && C >= AU_AUTO_MIN_C);
 }
 
 int activation1d_nlc_umma(const void* x, int x_dtype, void* y, int y_dtype, const float* alpha, const float* beta, int64_t B,
