@@ -231,6 +231,21 @@ BVG_API int bvg_forward(const bvg_model_desc* m_host, const float* mel, int64_t 
 BVG_API int bvg_forward_pcm16(const bvg_model_desc* m_host, const float* mel, int64_t mel_stride_b, int64_t mel_stride_c,
                       int16_t* pcm, int64_t B, int64_t T_mel, void* workspace, size_t workspace_bytes, void* stream);
 
+/* bvg_forward for callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * Same arguments and result as bvg_forward, minus the workspace: the plan's scratch lives in a static device array of
+ * BVG_NOALLOC_SCRATCH_BYTES inside the library (every GPU that loads libbvg.so holds it until the process exits).  The
+ * call allocates nothing (no cudaMalloc / cudaFree / allocating library routine); call bvg_init() beforehand if even the
+ * host-side stream / event handles of the plan must exist before the first call.
+ *  - Limit: bvg_workspace_bytes(m, B, T_mel) <= BVG_NOALLOC_SCRATCH_BYTES, else BVG_ERR_WORKSPACE with both numbers in
+ *    bvg_last_error() (22 kHz generator: about 300 mel frames per call in BVG_BF16_TC, 130 in BVG_F32_SPLIT_TC).
+ *  - All calls on a device share the one array.  Nothing in it has to start at zero (each plan buffer is written in
+ *    full before it is read), so contents left by the previous call are harmless -- but two calls whose GPU work
+ *    OVERLAPS (different streams, or graphs replayed concurrently) race on it: serialise them on one stream. */
+#define BVG_NOALLOC_SCRATCH_BYTES (64u << 20)
+BVG_API int bvg_forward_noalloc(const bvg_model_desc* m_host, const float* mel, int64_t mel_stride_b, int64_t mel_stride_c,
+                        float* wav, int64_t B, int64_t T_mel, void* stream);
+
 /* ---------------------------------------------------------------------------------------------------------- */
 /* v1 generator (indextts/BigVGAN/models.py:130-258 BigVGAN.forward after the speaker encoder): the same stack with a
  * per-utterance conditioning vector added after conv_pre (:236) and after every transposed conv (:244-245), and a

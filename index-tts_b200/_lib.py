@@ -14,6 +14,7 @@ if os.environ.get("BVG_LIB_PATH"):  # developer A/B of kernel build variants (to
     LIB_PATH = os.environ["BVG_LIB_PATH"]
 
 BVG_F32, BVG_BF16, BVG_I16, BVG_BF16X3 = 0, 1, 2, 3
+NOALLOC_SCRATCH_BYTES = 64 << 20  # BVG_NOALLOC_SCRATCH_BYTES (include/bvg.h): scratch limit of bvg_forward_noalloc
 BVG_EXACT_F32, BVG_BF16_TC, BVG_F32_SPLIT_TC = 0, 1, 2
 SPLIT_TERMS = 6  # term slots of a BVG_BF16X3 tensor (include/bvg.h)
 MAX_STAGES, MAX_KERNELS, MAX_DILATIONS, MAX_PHASES = 8, 4, 4, 8
@@ -87,6 +88,7 @@ SIGNATURES = {
     "bvg_forward_pcm16": (c_int, [C.POINTER(ModelDesc), c_vp, c_i64, c_i64, c_vp, c_i64, c_i64, c_vp, c_sz, c_vp]),
     "bvg_workspace_bytes": (c_sz, [C.POINTER(ModelDesc), c_i64, c_i64]),
     "bvg_forward": (c_int, [C.POINTER(ModelDesc), c_vp, c_i64, c_i64, c_vp, c_i64, c_i64, c_vp, c_sz, c_vp]),
+    "bvg_forward_noalloc": (c_int, [C.POINTER(ModelDesc), c_vp, c_i64, c_i64, c_vp, c_i64, c_i64, c_vp]),
     "bvg_forward_profile": (c_int, [C.POINTER(ModelDesc), c_vp, c_i64, c_i64, c_vp, c_i64, c_i64, c_vp, c_sz, c_vp,
                                     C.POINTER(LaunchRecord), c_int, C.POINTER(c_int)]),
     "bvg_forward_cond_profile": (c_int, [C.POINTER(ModelDesc), c_vp, c_int, c_i64, c_i64, C.POINTER(c_vp), c_vp, c_i64, c_i64,

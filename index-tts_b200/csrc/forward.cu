@@ -2,6 +2,7 @@
 #include "bvg_common.cuh"
 
 #include <cstdlib>
+#include <atomic>
 #include <vector>
 
 namespace bvg {
@@ -522,6 +523,56 @@ extern "C" int bvg_forward_pcm16(const bvg_model_desc* m, const float* mel, int6
                                  void* stream) {
     return forward_impl(m, mel, 0, mel_stride_b, mel_stride_c, nullptr, pcm, BVG_I16, B, T_mel, workspace, workspace_bytes,
                         stream);
+}
+
+// ---- bvg_forward without a caller workspace ---------------------------------------------------------------------
+// For callers that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc): the plan's
+// workspace lives in a file-scope device array of BVG_NOALLOC_SCRATCH_BYTES, held by every GPU that loads the library.
+// The array's name is only a host-side stand-in here; its device address comes from cudaGetSymbolAddress, looked up once
+// per device with that device current.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[BVG_NOALLOC_SCRATCH_BYTES];
+
+namespace bvg {
+static int noalloc_scratch_ptr(void** out) {
+    constexpr int kMaxDevices = 64;
+    static std::atomic<void*> cache[kMaxDevices];
+    int dev = 0;
+    BVG_CUDA(cudaGetDevice(&dev));
+    BVG_REQUIRE(dev >= 0 && dev < kMaxDevices, BVG_ERR_UNSUPPORTED, "bvg_forward_noalloc: device ordinal %d >= %d", dev,
+                kMaxDevices);
+    void* p = cache[dev].load(std::memory_order_acquire);
+    if (p == nullptr) {
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (e != cudaSuccess || p == nullptr)
+            return set_error(BVG_ERR_CUDA, "bvg_forward_noalloc: cudaGetSymbolAddress on device %d: %s", dev,
+                             cudaGetErrorString(e));
+        cache[dev].store(p, std::memory_order_release);
+    }
+    *out = p;
+    return BVG_OK;
+}
+}  // namespace bvg
+
+extern "C" int bvg_forward_noalloc(const bvg_model_desc* m, const float* mel, int64_t mel_stride_b, int64_t mel_stride_c,
+                                   float* wav, int64_t B, int64_t T_mel, void* stream) {
+    BVG_REQUIRE(m && mel && wav, BVG_ERR_INVALID, "bvg_forward_noalloc: null pointer");
+    BVG_REQUIRE(B >= 0 && T_mel >= 0, BVG_ERR_INVALID, "bvg_forward_noalloc: negative shape");
+    if (B == 0 || T_mel == 0) return BVG_OK;
+    Plan pl;
+    int rc = make_plan(m, B, T_mel, &pl);
+    if (rc != BVG_OK) return rc;
+    BVG_REQUIRE(pl.total <= (size_t)BVG_NOALLOC_SCRATCH_BYTES, BVG_ERR_WORKSPACE,
+                "bvg_forward_noalloc: B=%lld, T_mel=%lld needs %zu bytes of scratch, the built-in array holds %zu "
+                "(use bvg_forward with a caller workspace for larger inputs)",
+                (long long)B, (long long)T_mel, pl.total, (size_t)BVG_NOALLOC_SCRATCH_BYTES);
+    void* scratch = nullptr;
+    rc = noalloc_scratch_ptr(&scratch);
+    if (rc != BVG_OK) return rc;
+    // Nothing has to start at zero: every buffer of the plan is written in full by its producer before any consumer reads
+    // it, and rows outside [0, T) come from TMA zero fill / clamped indices, never from memory -- what the previous call
+    // left in the array is not read.
+    return forward_impl(m, mel, 0, mel_stride_b, mel_stride_c, nullptr, wav, BVG_F32, B, T_mel, scratch,
+                        (size_t)BVG_NOALLOC_SCRATCH_BYTES, stream);
 }
 
 extern "C" int bvg_forward_profile(const bvg_model_desc* m, const float* mel, int64_t mel_stride_b, int64_t mel_stride_c,
