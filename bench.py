@@ -16,6 +16,8 @@ Printed JSON line (rank 0):
              kernels, all host threads) on a bounded sample: two of the batch's 16 utterances.  Falls back to the oracle
              port (oracle/torch_port.py, kind "port") when baseline/_ref is absent
   parity     SNR / max-abs of the TIMED output tensor against those two reference runs (same weights)
+  fp32_mode  the fp32 parity mode (bf16x3 split operands on tcgen05): cfg1-shape latency, its roofline fractions and
+             the waveform error of utterance 0 against the same reference run
 --impl reference: the CPU arm only, K timed steps after W warm-up steps, one 10 s utterance of the batch per step
 (utterances are independent, so audio-s/s of the sample is the metric of the workload); same metric/config/unit.
 """
@@ -473,7 +475,7 @@ def main():
 
     # ---- CPU baseline + parity of the TIMED tensor: the reference's own forward (fp32, host cores, same weights) on two
     # of the 16 utterances of the timed batch; the same two runs are the timed CPU baseline (bounded sample).
-    cpu, parity = None, None
+    cpu, parity, outs = None, None, None
     if not args.no_cpu_baseline:
         import numpy as np
         with contextlib.redirect_stdout(sys.stderr):
@@ -499,6 +501,54 @@ def main():
                       "utterances": picks, "snr_db": min(snrs), "snr_db_each": snrs, "max_abs": max(errs),
                       "bar_snr_db": bar, "ok": bool(min(snrs) >= bar and (args.precision == "bf16" or max(errs) <= 1e-4))}
 
+    # ---- fp32 parity mode (the precision the reference runs the path in, infer_v2.py:830-831, 860): bf16x3 split
+    # operands on the tcgen05 conv kernel (BVG_F32_SPLIT_TC).  cfg1 shape latency, its per-layer roofline (a conv's
+    # tensor-core ceiling is the bf16 peak / 6 partial products; bytes at 4 B per element) and the waveform error
+    # against the unmodified reference on utterance 0 of the timed batch.
+    fp32_mode = None
+    if world == 1:
+        model.set_precision("fp32")
+        mel1 = torch.randn(1, NUM_MELS, 431, generator=torch.Generator().manual_seed(0)).to(dev)
+        f1 = lambda: model(mel1)
+        with torch.no_grad():
+            for _ in range(3):
+                f1()
+            ms32_eager = timed(f1, 10)
+            model.set_cuda_graphs(4096)
+            for _ in range(3):
+                f1()
+            ms32_graph = timed(f1, 10)
+            model.set_cuda_graphs(0)
+        for _ in range(2):
+            B.profile_forward(model, mel1)
+        _, recs32 = B.profile_forward(model, mel1)
+        tf32_peak = peaks["tf_sus"] / 6.0
+        roof32 = sum(max(r["flops"] / (tf32_peak * 1e12), r["bytes"] / (peaks["hbm"] * 1e9)) * 1e3
+                     for r in recs32 if r["kind"] != "layout")
+        meas32 = sum(r["ms"] for r in recs32 if r["kind"] != "layout")
+        conv32 = [r for r in recs32 if r["kind"] in ("conv1d", "convtranspose1d")]
+        conv32_ms = sum(r["ms"] for r in conv32)
+        ach32 = sum(r["flops"] for r in conv32) / (conv32_ms * 1e-3) / 1e12 if conv32_ms > 0 else 0.0
+        par32 = None
+        if cpu is not None and parity is not None:
+            import numpy as np
+            with torch.no_grad():
+                w32 = model(mel_dev[0:1])[0].float().cpu().numpy().astype(np.float64).ravel()
+            refw = outs[0][0].numpy().astype(np.float64).ravel()
+            e32 = w32 - refw
+            par32 = {"utterance": 0, "max_abs": float(np.abs(e32).max()),
+                     "snr_db": 10.0 * float(np.log10((refw ** 2).sum() / max((e32 ** 2).sum(), 1e-300)))}
+            par32["ok"] = bool(par32["max_abs"] <= 1e-4 and par32["snr_db"] >= 80.0)
+        fp32_mode = {"workload": "cfg1 shape: 1 x 5 s mel (80x431), fp32 parity mode (bf16x3 split operands on tcgen05)",
+                     "eager_ms": ms32_eager, "cuda_graph_ms": ms32_graph,
+                     "audio_s_per_s_graph": (431 * HOP / SR) / (ms32_graph * 1e-3),
+                     "roofline": {"bound": "tensor", "achieved": ach32, "peak": tf32_peak, "unit": "TFLOP/s (fp32-equivalent)",
+                                  "frac": ach32 / tf32_peak, "peak_source": "sustained bf16 peak / 6 partial products"},
+                     "per_layer_roofline": {"roofline_ms": roof32, "measured_ms": meas32,
+                                            "frac": roof32 / meas32 if meas32 > 0 else None, "launches": len(recs32)},
+                     "parity": par32}
+        model.set_precision(args.precision)
+
     line = {
         "metric": "vocoder audio-sec/sec (RTF^-1)", "value": world * audio_s / (ms_step * 1e-3), "unit": "audio-s/s",
         "n_gpus": world, "steps": args.steps, "warmup": W, "ms_per_step": ms_step, "higher_is_better": True,
@@ -518,6 +568,7 @@ def main():
         "long_form": long_form,
         "v1_generator": v1_line,
         "latency": latency,
+        "fp32_mode": fp32_mode,
         "cpu_baseline": cpu,
         "parity": parity,
     }

@@ -585,22 +585,18 @@ static int launch_act_umma(const void* x, void* y, const float* alpha, const flo
     return launch_act_umma_cs<TIn, TOut, 0>(p, grid, st);
 }
 
-// BVG_ACT_UMMA: "0" keeps the SIMT kernel everywhere, "1" takes every shape the tensor-core kernel supports (A/B runs);
-// unset = automatic: rows of at least AU_AUTO_MIN_C channels.  Narrow rows (C = 24 / 48: 48- and 96-byte rows) make the
-// per-lane global accesses of this kernel scalar and strided, and it loses to the SIMT kernel there (r02: 186 vs 129 us
-// at C = 24); from C = 96 up it is level or ahead (115 vs 129 us at C = 384, f32 -> bf16).
-constexpr int64_t AU_AUTO_MIN_C = 96;
-static int act_umma_mode() {
-    static const int v = []() {
+// Opt-in (BVG_ACT_UMMA=1).  Measured on B200 at the cfg2 stage shapes (profiles/r02_act1d_simt_vs_umma.jsonl): level with
+// the SIMT kernel for fp32 input at C = 96..384 (126-127 vs 129-130 us), 4-6 % behind for bf16 input, and well behind at
+// C = 24 (188 vs 131 us: 48-byte rows make this kernel's per-lane global accesses scalar and strided).  The empty
+// pipeline (no cosine, no global traffic) already takes 79 us -- every U and Y element crosses the tensor-memory read
+// port -- so the SIMT kernel stays the default; DESIGN.md 4 has the attribution.
+bool act_umma_requested(int64_t C) {
+    (void)C;
+    static const bool v = []() {
         const char* e = getenv("BVG_ACT_UMMA");
-        if (e == nullptr || e[0] == '\0') return 2;
-        return e[0] == '0' ? 0 : 1;
+        return e != nullptr && e[0] == '1';
     }();
     return v;
-}
-bool act_umma_requested(int64_t C) {
-    const int m = act_umma_mode();
-    return m == 1 || (m == 2 && C >= AU_AUTO_MIN_C);
 }
 
 int activation1d_nlc_umma(const void* x, int x_dtype, void* y, int y_dtype, const float* alpha, const float* beta, int64_t B,

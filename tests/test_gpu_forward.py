@@ -312,3 +312,37 @@ def test_cuda_graph_replay_cache_is_bit_identical(full_models):
         finally:
             m.set_cuda_graphs(0)
             m.set_precision("fp32")
+
+
+def test_cfg2_full_batch_vs_oracle(full_models):
+    """BASELINE.json configs[1] at full size (16 x 862 frames, the bench workload) through BigVGAN.forward: the
+    oracle checks one utterance end to end; the other fifteen are checked through batch independence (every utterance of
+    the batched call equals its own B = 1 call to 1e-6 in fp32 mode, and stays on the bf16 bar in bf16 mode)."""
+    sd, m = full_models
+    g = torch.Generator().manual_seed(21)
+    mel = torch.randn(16, 80, 862, generator=g)
+    mel_d = mel.cuda()
+    m.set_precision("fp32")
+    with torch.no_grad():
+        wav32 = m(mel_d)
+    assert tuple(wav32.shape) == (16, 1, 862 * 256)
+    picks = [15]
+    refs = {i: O.forward(sd, mel[i:i + 1].numpy(), None, np.float32) for i in picks}
+    for i in picks:
+        _check_fp32(refs[i], wav32[i:i + 1].cpu().numpy(), f"cfg2 utterance {i}")
+    with torch.no_grad():
+        for i in range(16):
+            if i in picks:
+                continue
+            one = m(mel_d[i:i + 1])
+            assert float((one[0] - wav32[i]).abs().max()) <= 1e-6, f"utterance {i}: batched fp32 result differs from B = 1"
+    m.set_precision("bf16")
+    with torch.no_grad():
+        wav16 = m(mel_d)
+    for i in picks:
+        _check_bf16(refs[i], wav16[i:i + 1].float().cpu().numpy(), f"cfg2 utterance {i}")
+    ref32 = wav32.cpu().numpy().astype(np.float64)
+    got16 = wav16.float().cpu().numpy()
+    for i in range(16):
+        assert snr_db(ref32[i], got16[i]) >= 40.0, f"utterance {i} in bf16 mode"
+    m.set_precision("fp32")

@@ -57,6 +57,38 @@ def test_activation1d_ncl_vs_oracle(ops, T, dtype):
         assert snr_db(ref, y) > 45
 
 
+@pytest.mark.parametrize("T", [2 ** 21, 2 ** 20 + 37])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_activation1d_ncl_cfg3_full_size(ops, T, dtype):
+    """BASELINE.json configs[2] at full size: the public [B, C, T] op at C = 1536, T = 2^21 (aligned) and 2^20 + 37 (odd
+    rows -> unaligned path).  The oracle checks the first and last 4096 samples of a few channels (the op is local: an
+    output depends on x within +-6 samples, so a slice with a 64-sample margin reproduces it exactly), plus a window that
+    straddles a tile boundary in the middle; a checksum over every channel guards against rows that were never written."""
+    C = 1536
+    g = torch.Generator(device="cuda").manual_seed(T % 1000)
+    x = (1.5 * torch.randn(1, C, T, device="cuda", generator=g)).to(dtype)
+    al = 0.5 * torch.randn(C, device="cuda", generator=g)
+    be = 0.5 * torch.randn(C, device="cuda", generator=g)
+    y = ops.activation1d(x, al, be, dtype == torch.float32)
+    torch.cuda.synchronize()
+    assert y.dtype == dtype and tuple(y.shape) == (1, C, T)
+    assert bool(torch.isfinite(y.float().sum(dim=2)).all())   # every row written with finite values
+    chans = [0, 1, 767, 1534, 1535]
+    n, margin = 4096, 64
+    mid = (T // 2 // 2048) * 2048 - n // 2   # window across a 2048-sample tile edge
+    for lo, hi, keep_lo, keep_hi in ((0, n + margin, 0, n), (T - n - margin, T, T - n, T), (mid - margin, mid + n + margin, mid, mid + n)):
+        xs = x[0, chans, lo:hi].float().cpu().numpy().astype(np.float64)[None]
+        ref = O.activation1d(xs, al[chans].cpu().numpy(), be[chans].cpu().numpy())[0][:, keep_lo - lo:keep_hi - lo]
+        got = y[0, chans, keep_lo:keep_hi].float().cpu().numpy()
+        if dtype == torch.float32:
+            np.testing.assert_allclose(got, ref, rtol=0, atol=2e-5)
+        else:
+            assert rel_err(ref, got) < 2.0 ** -7
+            assert snr_db(ref, got) > 45
+    del x, y
+    torch.cuda.empty_cache()
+
+
 def test_activation1d_ncl_fast_math_fp32(ops):
     """MUFU path on fp32 IO: absolute error of cos.approx (~5e-7 * 1/b) -> max-abs <= 5e-5 for these inputs."""
     rng = np.random.default_rng(3)
@@ -432,3 +464,18 @@ def test_conv1d_cluster_multicast_mode_subprocess():
     out = subprocess.run([sys.executable, os.path.join(root, "tools", "conv_cluster_check.py")], capture_output=True, text=True,
                          timeout=300, env=env)
     assert out.returncode == 0 and "ALL OK" in out.stdout and "cluster=1" in out.stdout, out.stdout[-1500:] + out.stderr[-1500:]
+
+
+def test_activation1d_tensor_core_kernel_opt_in():
+    """csrc/act1d_umma.cu (both FIRs on tcgen05, A operand in tensor memory) is opt-in (BVG_ACT_UMMA=1, read once per
+    process): run the developer check -- NumPy oracle on small shapes, range-reduced SIMT kernel on large ones, 45 dB bar
+    for bf16 output and 60 dB for fp32 output -- in a child process with the switch on."""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, BVG_ACT_UMMA="1")
+    r = subprocess.run([sys.executable, os.path.join(root, "tools", "act_umma_check.py")], env=env, capture_output=True,
+                       text=True, timeout=600)
+    print(r.stdout[-1500:])
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+    assert "CHECK ok" in r.stdout

@@ -1,7 +1,7 @@
 """Developer tool: the tensor-core Activation1d kernel (csrc/act1d_umma.cu) against the NumPy oracle (small shapes) and the
 range-reduced SIMT kernel (large shapes), plus CUDA-event timings of the stage shapes of cfg2.
 
-    python tools/act_umma_check.py [--time]          (BVG_ACT_UMMA=0 times the SIMT kernel instead)
+    python tools/act_umma_check.py [--time]          (run with BVG_ACT_UMMA=1; without it the SIMT kernel is timed)
 """
 import argparse, json, os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -72,7 +72,7 @@ if a.time:
             ms /= 5
             nbytes = B * T * C * (x.element_size() + y.element_size())
             row = dict(C=C, T=T, B=B, io=f"{str(in_dt)[6:]}->{str(out_dt)[6:]}", us=ms * 1e3, GBs=nbytes / ms / 1e6,
-                       umma=os.environ.get("BVG_ACT_UMMA", "1"))
+                       umma=os.environ.get("BVG_ACT_UMMA", "0"))
             rows.append(row)
             print(json.dumps(row), flush=True)
 sys.exit(1 if bad else 0)
