@@ -473,6 +473,29 @@ def main():
         latency = {"workload": "cfg1 shape: 1 x 5 s mel (80x431), " + args.precision, "eager_ms": ms_eager,
                    "cuda_graph_ms": ms_graph, "audio_s_per_s_graph": (431 * HOP / SR) / (ms_graph * 1e-3)}
 
+    # ---- cfg3 point (BASELINE.json configs[2]): the public [B, C, T] Activation1d op (north_star (a)) at C = 1536,
+    # T = 2^21, both I/O dtypes, isolated, L2 flushed between launches; algorithmic bytes = one read + one write.
+    act_op = None
+    if world == 1:
+        act_op = {"workload": "cfg3: Activation1d [1, 1536, 2^21], isolated launch, 256 MiB L2 flush between launches",
+                  "hbm_peak_GBs": peaks["hbm"], "points": []}
+        Cc, Tc = 1536, 1 << 21
+        alc = 0.5 * torch.randn(Cc, device=dev)
+        bec = 0.5 * torch.randn(Cc, device=dev)
+        # sine modes: "fast" = MUFU cos (what the bf16 forward uses), "precise" = range-reduced sinf (fp32 parity mode)
+        for dt, name, prec_c in ((torch.float32, "f32", False), (torch.float32, "f32", True), (torch.bfloat16, "bf16", False)):
+            xc = torch.randn(1, Cc, Tc, device=dev).to(dt)
+            fc = lambda: ops.activation1d(xc, alc, bec, prec_c)
+            for _ in range(2):
+                yc = fc()
+            ms_c = timed(fc, 5)
+            nbytes = 2.0 * xc.numel() * xc.element_size()
+            act_op["points"].append({"dtype": name, "sine": "precise" if prec_c else "fast", "ms": ms_c, "algorithmic_GBs": nbytes / (ms_c * 1e-3) / 1e9,
+                                     "frac_of_hbm_peak": nbytes / (ms_c * 1e-3) / 1e9 / peaks["hbm"],
+                                     "Gelem_per_s": xc.numel() / (ms_c * 1e-3) / 1e9})
+            del xc, yc
+        torch.cuda.empty_cache()
+
     # ---- CPU baseline + parity of the TIMED tensor: the reference's own forward (fp32, host cores, same weights) on two
     # of the 16 utterances of the timed batch; the same two runs are the timed CPU baseline (bounded sample).
     cpu, parity, outs = None, None, None
@@ -569,6 +592,7 @@ def main():
         "v1_generator": v1_line,
         "latency": latency,
         "fp32_mode": fp32_mode,
+        "activation1d_op": act_op,
         "cpu_baseline": cpu,
         "parity": parity,
     }

@@ -745,12 +745,19 @@ static int launch_nlc(const void* x, void* y, const float* alpha, const float* b
     dim3 grid(static_cast<unsigned>(ceil_div(n_seg, segs_per_block)), static_cast<unsigned>(P / S),
               static_cast<unsigned>(B));
     dim3 block(S * segs_per_block);
+    // developer knob: unused dynamic shared memory per CTA caps the CTAs per SM (how many warps does the FMA pipe need?)
+    static const int pad_kb = []() { const char* e = getenv("BVG_ACT_DIRECT_SMEM_KB"); return e ? atoi(e) : 0; }();
+    const size_t pad = (size_t)pad_kb * 1024;
+    if (pad > 0) {
+        cudaFuncSetAttribute(act1d_nlc_kernel<TIn, TOut, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pad);
+        cudaFuncSetAttribute(act1d_nlc_kernel<TIn, TOut, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pad);
+    }
     if (precise)
-        act1d_nlc_kernel<TIn, TOut, true><<<grid, block, 0, st>>>(static_cast<const TIn*>(x), static_cast<TOut*>(y),
-                                                                   alpha, beta, T, (int)C, L, S, n_seg);
+        act1d_nlc_kernel<TIn, TOut, true><<<grid, block, pad, st>>>(static_cast<const TIn*>(x), static_cast<TOut*>(y),
+                                                                     alpha, beta, T, (int)C, L, S, n_seg);
     else
-        act1d_nlc_kernel<TIn, TOut, false><<<grid, block, 0, st>>>(static_cast<const TIn*>(x), static_cast<TOut*>(y),
-                                                                    alpha, beta, T, (int)C, L, S, n_seg);
+        act1d_nlc_kernel<TIn, TOut, false><<<grid, block, pad, st>>>(static_cast<const TIn*>(x), static_cast<TOut*>(y),
+                                                                      alpha, beta, T, (int)C, L, S, n_seg);
     BVG_LAUNCH_CHECK("act1d_nlc_kernel");
     return BVG_OK;
 }

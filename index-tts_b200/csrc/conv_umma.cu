@@ -250,7 +250,13 @@ __device__ __forceinline__ void umma_issue_loop(const ConvUmmaParams& p, uint32_
     }
 }
 
+// -DBVG_CONV_MAXNREG=96 (developer A/B, tools/build_variant.sh): cap the registers so that a 384-thread conv CTA and a
+// 288-thread Activation1d CTA (96 registers) fit one SM's register file together.
+#ifdef BVG_CONV_MAXNREG
+__global__ void __maxnreg__(BVG_CONV_MAXNREG)
+#else
 __global__ void __launch_bounds__(UMMA_THREADS2, 1)
+#endif
 conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_w,
                  const __grid_constant__ CUtensorMap map_res, const __grid_constant__ CUtensorMap map_acc,
                  const __grid_constant__ CUtensorMap map_y32, const __grid_constant__ CUtensorMap map_y16,

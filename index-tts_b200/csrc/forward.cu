@@ -491,6 +491,10 @@ static int forward_impl(const bvg_model_desc* m, const float* mel, int mel_layou
         const double rows = (double)B * T;
         ProfScope ps(BVG_K_ACT, -1, C, C, 0, 0, B * T, 62.0 * rows * C, 2.0 * es * rows * C + 8.0 * C, st);
         float* R = reinterpret_cast<float*>(ws + pl.off_r[0]);
+        // same sine mode as the rest of the plan.  MUFU cos without range reduction was probed for this layer's worst case
+        // (tools/act_range_probe.py, profiles/r01_v8_act_range_probe.log: log-parameters up to +-4, arguments up to
+        // 4000 rad): within 4 dB of the range-reduced sinf path, both limited by the fp32 rounding of a*u that the
+        // reference shares; the precise path costs 2.7x on this launch (197 vs 526 G elements/s at cfg3).
         rc = activation1d_nlc(SUM, BVG_F32, R, BVG_F32, m->act_post.alpha_log, m->act_post.beta_log, B, T, C, precise, st);
     }
     if (rc != BVG_OK) return rc;

@@ -74,9 +74,20 @@ def _ensure_parent_packages():
                 setattr(sys.modules[".".join(parts[:i - 1])], parts[i - 1], stub)
 
 
-def install(preload_kernels: bool = True):
+def install(preload_kernels: bool = True, precision: str = None):
     """Alias this package as ``indextts.s2mel.modules.bigvgan`` and, for the v1 pipeline, ``indextts.BigVGAN`` (idempotent).  With ``preload_kernels`` the shared
-    library is loaded right away, so a missing ``libbvg.so`` fails here, loudly, instead of at the first forward."""
+    library is loaded right away, so a missing ``libbvg.so`` fails here, loudly, instead of at the first forward.
+
+    ``precision`` ("bf16" | "fp32" | "fp32_simt") sets the arithmetic of every generator constructed afterwards; the
+    reference runs this path in fp32 (infer_v2.py:830-831, 860), so the choice is logged either way: the default
+    (``$BVG_PRECISION`` or "bf16") trades exact fp32 for the bf16 tensor-core mode (>= 40 dB against the fp32 result)."""
+    import logging
+    from . import bigvgan as _bv, ops as _ops
+    if precision is not None:
+        _ops.precision_code(precision)  # validates the name
+        _bv.DEFAULT_PRECISION = precision
+    logging.getLogger("index_tts_b200").info("dropin.install: vocoder precision mode %r (the reference runs fp32; "
+                                             "set_precision() or install(precision=...) changes it)", _bv.DEFAULT_PRECISION)
     _ensure_parent_packages()
     table = [(REFERENCE_PACKAGE + rel, ours) for rel, ours in _ALIASES.items()]
     table += [(V1_REFERENCE_PACKAGE + rel, ours) for rel, ours in _V1_ALIASES.items()]

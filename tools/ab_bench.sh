@@ -4,7 +4,7 @@ OUT=gpurun_out/${TAG:-ab}; mkdir -p $OUT
 i=0
 for envs in "$@"; do
   i=$((i+1))
-  env $envs timeout 300 python bench.py --steps 5 --warmup 3 --no-cpu-baseline > $OUT/bench_$i.json 2> $OUT/bench_$i.err
+  env $envs timeout 300 python bench.py --steps 5 --warmup 3 --no-cpu-baseline --no-v1 > $OUT/bench_$i.json 2> $OUT/bench_$i.err
   python - "$envs" $OUT/bench_$i.json <<'PY'
 import json,sys
 try:

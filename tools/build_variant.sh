@@ -10,7 +10,7 @@ NVCC="${NVCC:-/usr/local/cuda/bin/nvcc}"
 "${NVCC}" -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -Xcompiler -fPIC,-fvisibility=hidden --expt-relaxed-constexpr \
   -Xptxas -v ${DEFS} -c "${ROOT}/index-tts_b200/csrc/${SRC}.cu" -o "${OBJ}/${SRC}_var.o" > "${OBJ}/${SRC}_var.log" 2>&1
 objs=()
-for f in api act1d act1d_umma conv_umma conv_simt pack cond forward; do
+for f in api act1d act1d_umma conv_umma conv_simt pack cond forward; do  # keep in step with csrc/build.sh
   if [ "$f" == "$SRC" ]; then objs+=("${OBJ}/${f}_var.o"); else objs+=("${OBJ}/${f}.o"); fi
 done
 "${NVCC}" -shared -o "${ROOT}/${OUT}" "${objs[@]}" -lcudart_static -ldl -lrt -lpthread
