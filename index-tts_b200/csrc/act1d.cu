@@ -590,6 +590,32 @@ struct NclIO<__nv_bfloat16> {
     static __device__ __forceinline__ void store1(__nv_bfloat16* y, float v) { *y = __float2bfloat16_rn(v); }
 };
 
+// xr[j] = tile[base4 + D + j], j < 32, base4 % 4 == 0, 0 < D < 4 (rows that start D floats into a 16-byte vector)
+template <int D>
+__device__ __forceinline__ void ncl_load32_shifted(const float* tile, int base4, float (&xr)[32]) {
+    const float4* p = reinterpret_cast<const float4*>(tile + base4);
+    float buf[36];
+#pragma unroll
+    for (int j = 0; j < 9; ++j) {
+        const float4 v = p[j];
+        buf[4 * j] = v.x; buf[4 * j + 1] = v.y; buf[4 * j + 2] = v.z; buf[4 * j + 3] = v.w;
+    }
+#pragma unroll
+    for (int j = 0; j < 32; ++j) xr[j] = buf[j + D];
+}
+// 16 fp32 outputs to a row address that is H floats short of a 16-byte boundary (0 < H < 4): H scalars, three aligned
+// vectors, 4 - H scalars.
+template <int H>
+__device__ __forceinline__ void ncl_store16_shifted(float* y, const float (&o)[16]) {
+#pragma unroll
+    for (int j = 0; j < H; ++j) y[j] = o[j];
+#pragma unroll
+    for (int v = 0; v < 3; ++v)
+        *reinterpret_cast<float4*>(y + H + 4 * v) = make_float4(o[H + 4 * v], o[H + 4 * v + 1], o[H + 4 * v + 2], o[H + 4 * v + 3]);
+#pragma unroll
+    for (int j = H + 12; j < 16; ++j) y[j] = o[j];
+}
+
 // grid = (ceil(T / NCL_TILE), C, B)
 template <typename TIO, bool PRECISE>
 __global__ void __launch_bounds__(NCL_THREADS)
@@ -633,7 +659,16 @@ act1d_ncl_kernel(const TIO* __restrict__ x, TIO* __restrict__ y, const float* __
             const int base = delta + static_cast<int>(i0 - 8 - lo);
             if (delta == 0) {
                 NclIO<TIO>::load32(tile, base, xr);
-            } else {  // row not 16-byte aligned (odd T): scalar shared-memory reads, still no index arithmetic per element
+            } else if (sizeof(TIO) == 4) {
+                // fp32 row that is not 16-byte aligned (odd T): the tile was copied from the aligned address below the row
+                // start, so this thread's window begins `delta` floats into a vector.  Nine aligned 128-bit reads and a
+                // compile-time register selection per alignment class instead of 32 scalar reads.
+                switch (delta) {
+                    case 1: ncl_load32_shifted<1>(reinterpret_cast<const float*>(tile), base - 1, xr); break;
+                    case 2: ncl_load32_shifted<2>(reinterpret_cast<const float*>(tile), base - 2, xr); break;
+                    default: ncl_load32_shifted<3>(reinterpret_cast<const float*>(tile), base - 3, xr); break;
+                }
+            } else {  // bf16 row not 16-byte aligned: scalar shared-memory reads, still no index arithmetic per element
 #pragma unroll
                 for (int j = 0; j < 32; ++j) xr[j] = NclIO<TIO>::get(tile, base + j);
             }
@@ -702,7 +737,27 @@ act1d_ncl_kernel(const TIO* __restrict__ x, TIO* __restrict__ y, const float* __
         }
         return;
     }
-    // Rows that are not 16-byte aligned (odd T): per-thread stores would be 16 scattered scalar writes per lane, so the
+    if (sizeof(TIO) == 4) {
+        // fp32 rows that are not 16-byte aligned: every thread's 64-byte span still contains three aligned vectors
+        if (active) {
+            float* yr = reinterpret_cast<float*>(yrow);
+            if (i0 + NCL_PER_THREAD <= T) {
+                const int h = static_cast<int>((4 - ((reinterpret_cast<uintptr_t>(yr) >> 2) & 3)) & 3);
+                switch (h) {
+                    case 0: NclIO<float>::store16(yr, out); break;
+                    case 1: ncl_store16_shifted<1>(yr, out); break;
+                    case 2: ncl_store16_shifted<2>(yr, out); break;
+                    default: ncl_store16_shifted<3>(yr, out); break;
+                }
+            } else {
+#pragma unroll
+                for (int q = 0; q < NCL_PER_THREAD; ++q)
+                    if (i0 + q < T) yr[q] = out[q];
+            }
+        }
+        return;
+    }
+    // bf16 rows that are not 16-byte aligned (odd T): per-thread stores would be 16 scattered scalar writes per lane, so the
     // tile is transposed through shared memory (one pad word per 32 keeps both phases bank-conflict free) and written
     // with fully coalesced scalar stores.
     __syncthreads();  // every thread has consumed its part of the input tile
