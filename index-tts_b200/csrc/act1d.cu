@@ -616,6 +616,64 @@ __device__ __forceinline__ void ncl_store16_shifted(float* y, const float (&o)[1
     for (int j = H + 12; j < 16; ++j) y[j] = o[j];
 }
 
+// out[q] = y[i0 + q], q < 16, from xr[j] = x[cl(i0 - 8 + j)].  EDGE: the thread touches an end of the row (replicate
+// padding of the activated 2x signal).
+template <bool PRECISE, bool EDGE>
+__device__ __forceinline__ void ncl_compute16(const float (&xr)[32], const SnakeCoef& coef, int64_t i0, int64_t T,
+                                              float (&out)[NCL_PER_THREAD]) {
+    const float e0 = 2.f * BVG_F0, e1 = 2.f * BVG_F1, e2 = 2.f * BVG_F2, e3 = 2.f * BVG_F3, e4 = 2.f * BVG_F4,
+                e5 = 2.f * BVG_F5;
+    // The packed up-sampler reads (x[a], x[a+1]) for every a: an FFMA2 operand is an even-aligned 64-bit register pair,
+    // so the odd-start pairs are materialised ONCE (30 MOVs) instead of being re-assembled at each of their six uses
+    // (ncu r02y: ~250 MOVs of 880 instructions per thread, issue slots 81 % busy against 67 % for the FMA pipe).
+    float2 xe[16], xo[15];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) xe[i] = make_float2(xr[2 * i], xr[2 * i + 1]);
+#pragma unroll
+    for (int i = 0; i < 15; ++i) xo[i] = make_float2(xr[2 * i + 1], xr[2 * i + 2]);
+#define NCL_X2(a) (((a) & 1) ? xo[(a) >> 1] : xe[(a) >> 1])
+    // v2[p] = (v[2m], v[2m+1]) for m = i0 - 3 + p
+    float2 v2[NCL_PER_THREAD + 6];
+    float vlast = 0.f;
+    // pairs with m >= T repeat v[2T-1]: in tile-relative 32-bit arithmetic (the row end is at most 2^31 away or irrelevant)
+    const int p_end = EDGE ? static_cast<int>(min(T - (i0 - 3), (int64_t)(NCL_PER_THREAD + 6))) : NCL_PER_THREAD + 6;
+#pragma unroll
+    for (int p = 0; p < NCL_PER_THREAD + 6; ++p) {
+        // x[m+j] = xr[p + 5 + j]
+        float2 u = fmul2(make_float2(e0, e1), NCL_X2(p + 2));
+        u = ffma2(make_float2(e2, e3), NCL_X2(p + 3), u);
+        u = ffma2(make_float2(e4, e5), NCL_X2(p + 4), u);
+        u = ffma2(make_float2(e5, e4), NCL_X2(p + 5), u);
+        u = ffma2(make_float2(e3, e2), NCL_X2(p + 6), u);
+        u = ffma2(make_float2(e1, e0), NCL_X2(p + 7), u);
+        float2 v = snake2<PRECISE>(u, coef);
+        if (EDGE) {
+            if (p >= p_end) {
+                v = splat(vlast);
+            } else {
+                vlast = v.y;
+            }
+        }
+        v2[p] = v;
+    }
+#undef NCL_X2
+    if (EDGE && i0 == 0) {  // m = -3,-2,-1 -> v[0]
+        v2[0] = v2[1] = v2[2] = splat(v2[3].x);
+    }
+    const float hoisted_c = PRECISE ? 0.f : coef.invb.x;
+#pragma unroll
+    for (int q = 0; q < NCL_PER_THREAD; ++q) {
+        float2 acc = fmul2(make_float2(BVG_F1, BVG_F2), v2[q + 1]);
+        acc = ffma2(make_float2(BVG_F3, BVG_F4), v2[q + 2], acc);
+        acc = ffma2(make_float2(BVG_F5, BVG_F5), v2[q + 3], acc);
+        acc = ffma2(make_float2(BVG_F4, BVG_F3), v2[q + 4], acc);
+        acc = ffma2(make_float2(BVG_F2, BVG_F1), v2[q + 5], acc);
+        float r = fmaf(BVG_F0, v2[q].y, acc.x);
+        r = fmaf(BVG_F0, v2[q + 6].x, r);
+        out[q] = r + acc.y + hoisted_c;
+    }
+}
+
 // grid = (ceil(T / NCL_TILE), C, B)
 template <typename TIO, bool PRECISE>
 __global__ void __launch_bounds__(NCL_THREADS)
@@ -685,45 +743,13 @@ act1d_ncl_kernel(const TIO* __restrict__ x, TIO* __restrict__ y, const float* __
         for (int j = 0; j < 32; ++j) xr[j] = 0.f;
     }
 
-    const float e0 = 2.f * BVG_F0, e1 = 2.f * BVG_F1, e2 = 2.f * BVG_F2, e3 = 2.f * BVG_F3, e4 = 2.f * BVG_F4,
-                e5 = 2.f * BVG_F5;
-    // v2[p] = (v[2m], v[2m+1]) for m = i0 - 3 + p
-    float2 v2[NCL_PER_THREAD + 6];
-    float vlast = 0.f;
-#pragma unroll
-    for (int p = 0; p < NCL_PER_THREAD + 6; ++p) {
-        // x[m+j] = xr[p + 5 + j]
-        float2 u = fmul2(make_float2(e0, e1), make_float2(xr[p + 2], xr[p + 3]));
-        u = ffma2(make_float2(e2, e3), make_float2(xr[p + 3], xr[p + 4]), u);
-        u = ffma2(make_float2(e4, e5), make_float2(xr[p + 4], xr[p + 5]), u);
-        u = ffma2(make_float2(e5, e4), make_float2(xr[p + 5], xr[p + 6]), u);
-        u = ffma2(make_float2(e3, e2), make_float2(xr[p + 6], xr[p + 7]), u);
-        u = ffma2(make_float2(e1, e0), make_float2(xr[p + 7], xr[p + 8]), u);
-        float2 v = snake2<PRECISE>(u, coef);
-        const int64_t m = i0 - 3 + p;
-        if (m >= T) {
-            v = splat(vlast);
-        } else {
-            vlast = v.y;
-        }
-        v2[p] = v;
-    }
-    if (i0 == 0) {  // m = -3,-2,-1 -> v[0]
-        v2[0] = v2[1] = v2[2] = splat(v2[3].x);
-    }
-    const float hoisted_c = PRECISE ? 0.f : coef.invb.x;
+    // interior threads (every activated pair m = i0-3 .. i0+18 lies inside the row) skip the replicate-padding logic of
+    // the 2x signal: no 64-bit compares and selects per pair
     float out[NCL_PER_THREAD];
-#pragma unroll
-    for (int q = 0; q < NCL_PER_THREAD; ++q) {
-        float2 acc = fmul2(make_float2(BVG_F1, BVG_F2), v2[q + 1]);
-        acc = ffma2(make_float2(BVG_F3, BVG_F4), v2[q + 2], acc);
-        acc = ffma2(make_float2(BVG_F5, BVG_F5), v2[q + 3], acc);
-        acc = ffma2(make_float2(BVG_F4, BVG_F3), v2[q + 4], acc);
-        acc = ffma2(make_float2(BVG_F2, BVG_F1), v2[q + 5], acc);
-        float r = fmaf(BVG_F0, v2[q].y, acc.x);
-        r = fmaf(BVG_F0, v2[q + 6].x, r);
-        out[q] = r + acc.y + hoisted_c;
-    }
+    if (i0 > 0 && i0 + NCL_PER_THREAD + 3 <= T)
+        ncl_compute16<PRECISE, false>(xr, coef, i0, T, out);
+    else
+        ncl_compute16<PRECISE, true>(xr, coef, i0, T, out);
     TIO* yrow = y + (b * C + c) * T + i0;
     if (vec_store_ok) {
         if (active) {

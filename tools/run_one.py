@@ -1,4 +1,4 @@
-"""Developer tool: one isolated launch for ncu.  python tools/run_one.py conv C T k d res | act C T in_dtype"""
+"""Developer tool: one isolated launch for ncu.  python tools/run_one.py conv C T k d res | act C T in_dtype | ncl C T dtype"""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
@@ -15,6 +15,13 @@ if kind == "conv":
     for _ in range(3):
         if res: ops.conv1d_nlc(x, w, bias, d, 1, residual=r)
         else: ops.conv1d_nlc(x, w, bias, d, 1, out_f32=False, out_bf16=True)
+elif kind == "ncl":  # the public [B, C, T] op, fast-sine mode
+    C, T = int(sys.argv[2]), int(sys.argv[3])
+    x = torch.randn(1, C, T, device="cuda")
+    if sys.argv[4] == "bf16": x = x.bfloat16()
+    al = 0.5 * torch.randn(C, device="cuda"); be = 0.5 * torch.randn(C, device="cuda")
+    for _ in range(3):
+        ops.activation1d(x, al, be, False)
 else:
     C, T = int(sys.argv[2]), int(sys.argv[3])
     x = torch.randn(B, T, C, device="cuda")
