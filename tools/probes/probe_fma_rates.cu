@@ -28,6 +28,9 @@ constexpr int ITERS = 2048;
 #define HFMA2_RR(a, b, c) asm volatile("fma.rn.f16x2 %0, %0, %1, %2;" : "+r"(a) : "r"(b), "r"(c))
 #define HFMA2_IMM(a, c) asm volatile("{.reg .b32 t; mov.b32 t, 0x3BFF3BFF; fma.rn.f16x2 %0, %0, t, %1;}" : "+r"(a) : "r"(c))
 #define BFMA2_RR(a, b, c) asm volatile("fma.rn.bf16x2 %0, %0, %1, %2;" : "+r"(a) : "r"(b), "r"(c))
+#define FFMA2_D3(d, a, b) asm volatile("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(d) : "l"(a), "l"(b))
+#define FFMA2_DIMM(d, a) asm volatile("{.reg .b64 t; mov.b64 t, 0x3F7FF0003F7FF000; fma.rn.f32x2 %0, %1, t, %0;}" : "+l"(d) : "l"(a))
+#define FFMA2_D4(d, a, b, c) asm volatile("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c))
 #define MUFU_COS(a) asm volatile("cos.approx.ftz.f32 %0, %0;" : "+f"(a))
 #define FADD2_RR(a, b) asm volatile("add.rn.f32x2 %0, %0, %1;" : "+l"(a) : "l"(b))
 #define FMUL2_RR(a, b) asm volatile("mul.rn.f32x2 %0, %0, %1;" : "+l"(a) : "l"(b))
@@ -38,6 +41,7 @@ __global__ void __launch_bounds__(1024, 1) rate_kernel(float seed, long long* cy
     float f[CH], g[CH];
     unsigned long long p[CH];
     unsigned h[CH];
+    unsigned long long q[CH], r[CH], w[CH];
     const float b = seed * 0.999f, c = seed * 1e-3f;
     unsigned long long pb, pc;
     asm volatile("mov.b64 %0, {%1, %1};" : "=l"(pb) : "f"(b));
@@ -49,6 +53,9 @@ __global__ void __launch_bounds__(1024, 1) rate_kernel(float seed, long long* cy
         g[i] = seed * 0.5f + i;
         asm volatile("mov.b64 %0, {%1, %2};" : "=l"(p[i]) : "f"(f[i]), "f"(g[i]));
         h[i] = 0x3C003C00u + i;
+        asm volatile("mov.b64 %0, {%1, %2};" : "=l"(q[i]) : "f"(f[i] * 1e-3f), "f"(g[i] * 1e-3f));
+        asm volatile("mov.b64 %0, {%1, %2};" : "=l"(r[i]) : "f"(g[i] * 1e-3f), "f"(f[i] * 1e-3f));
+        w[i] = 0;
     }
     __syncthreads();
     const long long t0 = clock64();
@@ -71,6 +78,10 @@ __global__ void __launch_bounds__(1024, 1) rate_kernel(float seed, long long* cy
                 case 12: FADD2_RR(p[i], pc); break;
                 case 13: FMUL2_RR(p[i], pb); break;
                 case 14: FFMA_RR(f[i], b, c); FFMA_RR(g[i], c, b); break;
+                case 15: FFMA2_D3(p[i], q[i], r[i]); break;                    // three distinct register pairs
+                case 16: FFMA2_DIMM(p[i], q[i]); break;                        // two register pairs + constant
+                case 17: FFMA2_D3(p[i], q[i], pb); break;                      // multiplier shared by all chains
+                case 18: FFMA2_D4(w[i], q[i], r[i], p[i]); break;              // four distinct pairs, no dependency
                 default: break;
             }
         }
@@ -82,6 +93,8 @@ __global__ void __launch_bounds__(1024, 1) rate_kernel(float seed, long long* cy
         float lo, hi;
         asm volatile("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(p[i]));
         acc += f[i] + g[i] + lo + hi + __uint_as_float(h[i]);
+        asm volatile("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(w[i]));
+        acc += lo + hi;
     }
     if (acc == 123.456f) sink[0] = acc;
     if (threadIdx.x == 0) cyc[blockIdx.x] = t1 - t0;
@@ -108,6 +121,10 @@ static void launch_mode(int mode, int sms, int threads, long long* dcyc, float* 
         case 12: launch<12>(sms, threads, dcyc, dsink); break;
         case 13: launch<13>(sms, threads, dcyc, dsink); break;
         case 14: launch<14>(sms, threads, dcyc, dsink); break;
+        case 15: launch<15>(sms, threads, dcyc, dsink); break;
+        case 16: launch<16>(sms, threads, dcyc, dsink); break;
+        case 17: launch<17>(sms, threads, dcyc, dsink); break;
+        case 18: launch<18>(sms, threads, dcyc, dsink); break;
         default: break;
     }
 }
@@ -124,6 +141,9 @@ int main() {
         {0, "FFMA reg,reg (scalar fp32)", 1, 1},
         {1, "FFMA with an immediate multiplier", 1, 1},
         {2, "FFMA2 (fma.rn.f32x2)", 2, 1},
+        {15, "FFMA2 d = a*b + d, three distinct pairs", 2, 1},
+        {16, "FFMA2 d = a*const + d", 2, 1},
+        {17, "FFMA2 d = a*B + d, B shared", 2, 1},
         {3, "HFMA2 reg,reg (fma.rn.f16x2)", 2, 1},
         {4, "HFMA2 with an immediate multiplier", 2, 1},
         {10, "HFMA2.BF16 (fma.rn.bf16x2)", 2, 1},
