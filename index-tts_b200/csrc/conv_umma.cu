@@ -847,7 +847,10 @@ int conv_umma_launch(const void* x, const void* w_packed, const float* bias, con
     static const int cluster_env = []() { const char* e = getenv("BVG_CONV_CLUSTER"); return e ? atoi(e) : 0; }();
     p.cluster = 0;
     // BVG_CONV_CLUSTER=2: every weight-streaming single-pipeline layer, whatever its size (experiment)
-    if (cluster_env && !p.stationary && p.ng == 1 && p.mp == 1 && num_phases == 1 && p.n_tile % 16 == 0 && p.m_tiles >= 2 &&
+    // BVG_CONV_CLUSTER=3 (experiment): also the pair-mode layers (C = 96 class with k >= 7), whose 264 KB of weights per
+    // 256-row tile make them L2-bound (gpurun r02t: 96 cycles per MMA against a 56-66-cycle issue floor)
+    if (cluster_env && !p.stationary && p.ng == 1 && (p.mp == 1 || cluster_env >= 3) && num_phases == 1 &&
+        p.n_tile % 16 == 0 && p.m_tiles >= 2 &&
         (cluster_env >= 2 || (Cin >= 256 && p.total_tiles <= 2 * (int64_t)device_sm_count()))) {
         p.cluster = 1;
         p.m_tiles = ceil_div(p.m_tiles, 2);  // the kernel walks row-tile PAIRS

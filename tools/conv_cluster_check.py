@@ -10,7 +10,8 @@ torch.backends.cuda.matmul.allow_tf32 = False
 flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 ok = True
 for (B, C, T, k, d, res) in [(1, 768, 1724, 11, 1, False), (1, 768, 1724, 3, 5, True), (1, 768, 1600, 7, 3, True), (1, 384, 6896, 11, 1, False),
-                             (1, 384, 6896, 7, 1, True), (2, 768, 700, 11, 5, False), (1, 768, 130, 3, 1, False), (1, 384, 257, 11, 3, True)]:
+                             (1, 384, 6896, 7, 1, True), (2, 768, 700, 11, 5, False), (1, 768, 130, 3, 1, False), (1, 384, 257, 11, 3, True),
+                             (16, 96, 55168, 11, 1, True), (16, 96, 55168, 7, 3, False), (3, 96, 1000, 11, 5, True), (16, 96, 55168, 7, 1, True)]:
     g = torch.Generator().manual_seed(C + T + k)
     x = torch.randn(B, T, C, generator=g).cuda().bfloat16()
     w = (torch.randn(C, C, k, generator=g) / (C * k) ** 0.5).cuda()
