@@ -91,6 +91,10 @@ struct ConvUmmaParams {
     int trace_n;
     uint32_t bias_smem;  // bytes of the zero-padded bias copy in shared memory (0: read the bias from global memory)
     float out_scale;
+    // dynamic tile scheduling: a zero-initialised counter in global memory (one per launch, owned by the caller's plan).  A CTA
+    // starts on tile blockIdx.x and takes tile gridDim.x + atomicAdd(counter, 1) next, so the kernel ends on the mean CTA
+    // instead of the slowest static share.  nullptr: static striding (tile = blockIdx.x + i * gridDim.x).
+    unsigned int* tile_ctr;
 };
 
 // Developer timeline: event e of pipeline role `slot` at the role's i-th tile (CTA 0 only).  Compiled in only with
@@ -139,6 +143,49 @@ struct TileWalker {
     }
 };
 
+// The tile sequence of a CTA as its consumer roles (UMMA issuer, epilogue warps, residual loader) see it.
+// Static: tile = first + i * step, decoded incrementally.  Dynamic (ConvUmmaParams::tile_ctr): the producer warp fetches
+// tile indices from the global counter, decodes them once and publishes {tile, n tile, m tile, batch} in a small
+// shared-memory queue; entry i belongs to pipeline group i % ng, the queue ends with one TQ_END entry per group.
+constexpr int TQ_SLOTS = 8;  // multiple of the number of pipeline groups
+constexpr uint32_t TQ_END = 0xffffffffu;
+struct TileFeed {
+    const uint4* q;
+    uint64_t* full;
+    uint64_t* empty;
+    uint32_t qi, qstride;  // dynamic: queue cursor of this role
+    uint32_t tile, step, total;
+    bool dyn, started;
+    TileWalker tw;
+    __device__ __forceinline__ TileFeed(bool dyn_, const uint4* q_, uint64_t* full_, uint64_t* empty_, uint32_t first_entry,
+                                        uint32_t entry_stride, uint32_t first, uint32_t step_, uint32_t total_,
+                                        uint32_t n_tiles, uint32_t m_tiles)
+        : q(q_), full(full_), empty(empty_), qi(first_entry), qstride(entry_stride), tile(first), step(step_), total(total_),
+          dyn(dyn_), started(false), tw(first, step_, n_tiles, m_tiles) {}
+    // whole-warp call; false when the sequence is exhausted
+    __device__ __forceinline__ bool next(TileCoord& c, int lane) {
+        if (!dyn) {
+            if (started) { tile += step; tw.next(); }
+            started = true;
+            if (tile >= total) return false;
+            c = tw.c;
+            return true;
+        }
+        const uint32_t slot = qi % TQ_SLOTS;
+        mbar_wait_warp(&full[slot], (qi / TQ_SLOTS) & 1u);
+        const uint4 e = q[slot];
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty[slot]);
+        qi += qstride;
+        if (e.x == TQ_END) return false;
+        tile = e.x;
+        c.nt = static_cast<int>(e.y);
+        c.mt = static_cast<int>(e.z);
+        c.b = static_cast<int>(e.w);
+        return true;
+    }
+};
+
 // tcgen05.mma with the 64-bit shared-memory descriptors assembled from a 32-bit cursor (start-address field, i.e.
 // byte address >> 4) and the constant upper half: advancing an operand is one 32-bit uniform add.
 __device__ __forceinline__ void umma_f16_lo(uint32_t d_tmem, uint32_t a_lo, uint32_t b_lo, uint32_t desc_hi,
@@ -164,7 +211,8 @@ template <bool STAT>
 __device__ __forceinline__ void umma_issue_loop(const ConvUmmaParams& p, uint32_t tmem_base, uint32_t sA_d, uint32_t sB_d,
                                                 uint64_t* a_full, uint64_t* a_empty, uint64_t* b_full, uint64_t* b_empty,
                                                 uint64_t* acc_full, uint64_t* acc_empty, int k_blocks, int n_tiles,
-                                                int group, uint32_t cta_first, uint32_t cta_step) {
+                                                int group, uint32_t cta_first, uint32_t cta_step, const uint4* tq,
+                                                uint64_t* tq_full, uint64_t* tq_empty, uint32_t m_tiles) {
     const uint32_t idesc = umma_idesc_bf16_f32(UMMA_BLOCK_M, p.n_tile);
     const uint32_t desc_hi = static_cast<uint32_t>(umma_desc_sw128_kmajor(0) >> 32);
     const uint32_t tap_step = static_cast<uint32_t>(p.dil) * 8u;  // dil rows * 128 B >> 4
@@ -191,14 +239,18 @@ __device__ __forceinline__ void umma_issue_loop(const ConvUmmaParams& p, uint32_
     if (STAT) mbar_wait_warp(&b_full[0], 0);
     uint32_t it = 0;
     const bool cluster = p.cluster != 0;
-    for (uint32_t tile = cta_first + group * cta_step; tile < total; tile += ng * cta_step, ++it) {
+    const int lane = static_cast<int>(threadIdx.x & 31u);
+    TileFeed tf(p.tile_ctr != nullptr, tq, tq_full, tq_empty, group, ng, cta_first + group * cta_step, ng * cta_step, total,
+                n_tiles, m_tiles);
+    TileCoord tcd;
+    for (; tf.next(tcd, lane); ++it) {
         mbar_wait_warp(&acc_empty[acc], pacc ^ 1);
         tc_fence_after_sync();
         if (leader) trace_ev(p, 1 + 6 * group, it);
         const uint32_t d_tmem = tmem_base + ((2 * group + acc) * mp) * n_tile;
         uint32_t accumulate = 0;
         uint32_t w_d = sB_d;  // stationary weight cursor
-        if (STAT && n_tiles > 1) w_d += (tile % static_cast<uint32_t>(n_tiles)) * w_tile_d;
+        if (STAT && n_tiles > 1) w_d += static_cast<uint32_t>(tcd.nt) * w_tile_d;
         for (int kb = 0; kb < k_blocks; ++kb) {
             const int k_steps = (kb + 1 == k_blocks) ? last_steps : 4;
             const bool k2 = k_steps > 1, k3 = k_steps > 2, k4 = k_steps > 3;
@@ -281,7 +333,10 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
     uint64_t* acc_empty = acc_full + 4;               // [2 per group]
     uint64_t* ld_full = acc_empty + 4;                // [UMMA_MAX_STAGES]
     uint64_t* ld_empty = ld_full + UMMA_MAX_STAGES;   // [UMMA_MAX_STAGES]
-    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(ld_empty + UMMA_MAX_STAGES);
+    uint64_t* tq_full = ld_empty + UMMA_MAX_STAGES;   // [TQ_SLOTS] tile queue (dynamic scheduling)
+    uint64_t* tq_empty = tq_full + TQ_SLOTS;          // [TQ_SLOTS]
+    uint4* tq = reinterpret_cast<uint4*>(tq_empty + TQ_SLOTS);
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tq + TQ_SLOTS);
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -306,6 +361,11 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
             mbar_init(&ld_full[i], 1); mbar_init(&ld_empty[i], 4);
         }
         for (int i = 0; i < 4; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 4); }
+        // a queue entry is read by its group's UMMA issuer, its four epilogue warps and (if it runs) the chunk loader
+        for (int i = 0; i < TQ_SLOTS; ++i) {
+            mbar_init(&tq_full[i], 1);
+            mbar_init(&tq_empty[i], 5 + ((p.has_res + p.has_acc) > 0 ? 1 : 0));
+        }
         fence_barrier_init();
     }
     if (p.bias_smem) {
@@ -354,8 +414,33 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
         uint32_t pa = 0, pa_other = 0, pb = 0, it = 0;
         TileWalker tw(cta_first, cta_step, n_tiles, m_tiles);
         const uint32_t b_half = p.b_stage_bytes >> 1;
-        for (uint32_t tile = cta_first; tile < total_tiles; tile += cta_step, ++it, tw.next()) {
-            const TileCoord tc = tw.c;
+        const bool dyn = p.tile_ctr != nullptr;
+        uint32_t tile = cta_first, nxt = 0, qi = 0;
+        int ends = 0;  // dynamic: end markers published (one per pipeline group)
+        for (;; ++it) {
+            TileCoord tc;
+            if (dyn) {
+                const bool valid = tile < total_tiles;
+                // the next tile index is fetched now: the atomic's round trip overlaps this tile's loads
+                if (valid && lane == 0) nxt = atomicAdd(p.tile_ctr, 1u) + gridDim.x;
+                tc = decode_tile(valid ? tile : 0u, n_tiles, m_tiles);
+                const uint32_t slot = qi % TQ_SLOTS;
+                mbar_wait_warp(&tq_empty[slot], ((qi / TQ_SLOTS) & 1u) ^ 1u);
+                if (lane == 0) {
+                    tq[slot] = make_uint4(valid ? tile : TQ_END, static_cast<uint32_t>(tc.nt), static_cast<uint32_t>(tc.mt),
+                                          static_cast<uint32_t>(tc.b));
+                    mbar_arrive(&tq_full[slot]);
+                }
+                __syncwarp();
+                ++qi;
+                if (!valid) {
+                    if (++ends == p.ng) break;
+                    continue;
+                }
+            } else {
+                if (tile >= total_tiles) break;
+                tc = tw.c;
+            }
             const int nt = tc.nt, mt = tc.mt * mt_mul + static_cast<int>(crank), b = tc.b;
             const int slot0 = g * a_per;
             const int phase = nt / p.tiles_per_phase;
@@ -396,6 +481,12 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                 uint32_t tp = pa; pa = pa_other; pa_other = tp;
                 g ^= 1;
             }
+            if (dyn) {
+                tile = __shfl_sync(0xffffffffu, nxt, 0);
+            } else {
+                tile += cta_step;
+                tw.next();
+            }
         }
     } else if (warp == 1 || warp == 7) {
         // ------------------------------ UMMA issuer (one per pipeline group) ------------------------------
@@ -403,10 +494,10 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
         const uint32_t sA_d = smem_u32(sA) >> 4, sB_d = smem_u32(sB) >> 4;
         if (p.stationary)
             umma_issue_loop<true>(p, tmem_base, sA_d, sB_d, a_full, a_empty, b_full, b_empty, acc_full, acc_empty, k_blocks,
-                                  n_tiles, group, cta_first, cta_step);
+                                  n_tiles, group, cta_first, cta_step, tq, tq_full, tq_empty, m_tiles);
         else
             umma_issue_loop<false>(p, tmem_base, sA_d, sB_d, a_full, a_empty, b_full, b_empty, acc_full, acc_empty,
-                                   k_blocks, n_tiles, group, cta_first, cta_step);
+                                   k_blocks, n_tiles, group, cta_first, cta_step, tq, tq_full, tq_empty, m_tiles);
     } else if (warp == 6) {
         // ------------------------------ residual / accum chunk loader ------------------------------
         if (n_ld > 0) {
@@ -416,9 +507,9 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
             const int ld_per = p.ld_stages / p.ng;
             int s = 0, s_other = 0, g = 0;
             uint32_t ps = 0, ps_other = 0;
-            TileWalker tw(cta_first, cta_step, n_tiles, m_tiles);
-            for (uint32_t tile = cta_first; tile < total_tiles; tile += cta_step, tw.next()) {
-                const TileCoord tc = tw.c;
+            TileFeed tf(p.tile_ctr != nullptr, tq, tq_full, tq_empty, 0u, 1u, cta_first, cta_step, total_tiles, n_tiles, m_tiles);
+            TileCoord tc;
+            while (tf.next(tc, lane)) {
                 const int nt = tc.nt, t00 = (tc.mt * mt_mul + static_cast<int>(crank)) * UMMA_BLOCK_M * p.mp, b = tc.b;
                 const int phase = nt / p.tiles_per_phase;
                 const int c0 = (nt % p.tiles_per_phase) * p.n_tile;
@@ -466,9 +557,10 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
         uint32_t pacc = 0, pls = 0;
         const bool tracer = (q == 0 && lane == 0);
         uint32_t it = 0;
-        TileWalker tw(cta_first + group * cta_step, p.ng * cta_step, n_tiles, m_tiles);
-        for (uint32_t tile = cta_first + group * cta_step; tile < total_tiles; tile += p.ng * cta_step, ++it, tw.next()) {
-            const TileCoord tc = tw.c;
+        TileFeed tf(p.tile_ctr != nullptr, tq, tq_full, tq_empty, static_cast<uint32_t>(group), static_cast<uint32_t>(p.ng),
+                    cta_first + group * cta_step, p.ng * cta_step, total_tiles, n_tiles, m_tiles);
+        TileCoord tc;
+        for (; tf.next(tc, lane); ++it) {
             const int nt = tc.nt, t00 = (tc.mt * mt_mul + static_cast<int>(crank)) * UMMA_BLOCK_M * p.mp, b = tc.b;
             const int phase = nt / p.tiles_per_phase;
             const int c0 = (nt % p.tiles_per_phase) * p.n_tile;  // channel offset inside the phase
@@ -695,7 +787,7 @@ int conv_umma_init() {
 int conv_umma_launch(const void* x, const void* w_packed, const float* bias, const float* residual, const float* accum,
                      float* y_f32, void* y_bf16, int64_t B, int64_t T, int64_t Cin, int64_t N, int64_t cout_phase,
                      int taps, int dil, const int* tap_base, int num_phases, float out_scale, cudaStream_t st,
-                     const float* cond) {
+                     const float* cond, unsigned int* tile_ctr) {
     BVG_REQUIRE(x && w_packed && (y_f32 || y_bf16), BVG_ERR_INVALID, "conv_umma: null pointer");
     BVG_REQUIRE(Cin % 8 == 0 && cout_phase % 8 == 0 && N == cout_phase * num_phases, BVG_ERR_UNSUPPORTED,
                 "conv_umma: Cin=%lld and Cout=%lld must be multiples of 8", (long long)Cin, (long long)cout_phase);
@@ -856,6 +948,13 @@ int conv_umma_launch(const void* x, const void* w_packed, const float* bias, con
         p.m_tiles = ceil_div(p.m_tiles, 2);  // the kernel walks row-tile PAIRS
         p.total_tiles = p.m_tiles * B * p.num_phases * p.tiles_per_phase;
     }
+
+    // Dynamic tile scheduling when the caller's plan provides a zeroed counter (forward.cu) and BVG_CONV_DYNAMIC=1 asks for it.
+    // Off by default: measured neutral to slightly slower on every cfg2 layer (profiles/r02_conv_dynamic_ab.log: conv sum
+    // 23.2 vs 22.9 ms) -- the 5-9 % spread of CTA durations is smaller than the cost of the queue hand-off and the atomics.
+    // Not in cluster mode (the two CTAs of a cluster must walk the same tiles) and pointless when every CTA has one tile.
+    static const int dyn_env = []() { const char* e = getenv("BVG_CONV_DYNAMIC"); return e ? atoi(e) : 0; }();
+    p.tile_ctr = (dyn_env && !p.cluster && p.total_tiles > device_sm_count()) ? tile_ctr : nullptr;
 
     CUtensorMap map_x, map_w, map_res, map_acc, map_y32, map_y16;
     // the A box is a_stage_bytes/128 rows so that expect_tx matches the bytes TMA writes

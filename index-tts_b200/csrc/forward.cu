@@ -9,7 +9,7 @@ namespace bvg {
 int conv_umma_launch(const void* x, const void* w_packed, const float* bias, const float* residual, const float* accum,
                      float* y_f32, void* y_bf16, int64_t B, int64_t T, int64_t Cin, int64_t N, int64_t cout_phase,
                      int taps, int dil, const int* tap_base, int num_phases, float out_scale, cudaStream_t st,
-                     const float* cond);
+                     const float* cond, unsigned int* tile_ctr);
 int conv_simt_launch(const void* x, const void* w_packed, const float* bias, const float* residual, const float* accum,
                      float* y_f32, void* y_bf16, int64_t B, int64_t T, int64_t Cin, int64_t N, int64_t cout_phase,
                      int taps, int dil, const int* tap_base, int num_phases, float out_scale, cudaStream_t st,
@@ -25,19 +25,36 @@ int add_channel_vector(const void* x, int x_dtype, const float* v, void* y, int 
                        cudaStream_t st);
 int split_rows(const float* x, void* y, int64_t rows, int64_t C, cudaStream_t st);
 
+// Tile counters for the conv kernel's dynamic scheduler: forward_impl carves an array of zeroed counter pairs out of the
+// caller's workspace and every tensor-core conv launch of that call takes the next one (the stand-alone conv entry points
+// have no workspace and keep static tile striding).  The cursor is per host thread and only set while a forward runs.
+constexpr int BVG_MAX_TILE_COUNTERS = 1024;
+struct TileCounterCursor {
+    unsigned int* base = nullptr;
+    int next = 0;
+};
+static thread_local TileCounterCursor t_tile_ctr;
+static unsigned int* take_tile_counter() {
+    if (t_tile_ctr.base == nullptr || t_tile_ctr.next >= BVG_MAX_TILE_COUNTERS) return nullptr;
+    return t_tile_ctr.base + 2 * (t_tile_ctr.next++);
+}
+struct TileCounterScope {  // clears the cursor on every exit path of forward_impl
+    ~TileCounterScope() { t_tile_ctr = TileCounterCursor(); }
+};
+
 static int conv_dispatch(int precision, const void* x, const void* w, const float* bias, const float* residual,
                          const float* accum, float* y_f32, void* y_bf16, int64_t B, int64_t T, int64_t Cin, int64_t N,
                          int64_t cout_phase, int taps, int dil, const int* tap_base, int num_phases, float out_scale,
                          cudaStream_t st, const float* cond = nullptr) {
     if (precision == BVG_BF16_TC)
         return conv_umma_launch(x, w, bias, residual, accum, y_f32, y_bf16, B, T, Cin, N, cout_phase, taps, dil, tap_base,
-                                num_phases, out_scale, st, cond);
+                                num_phases, out_scale, st, cond, take_tile_counter());
     if (precision == BVG_F32_SPLIT_TC) {
         // fp32 parity mode: x and w are bf16x3 split tensors (six term slots of Cin channels each on the K axis of the
         // same kernel, bvg_common.cuh); fp32 accumulation in TMEM, fp32 outputs only
         BVG_REQUIRE(y_bf16 == nullptr && y_f32 != nullptr, BVG_ERR_INVALID, "split-operand conv: the output is fp32");
         return conv_umma_launch(x, w, bias, residual, accum, y_f32, nullptr, B, T, Cin * BVG_SPLIT_TERMS, N, cout_phase, taps,
-                                dil, tap_base, num_phases, out_scale, st, cond);
+                                dil, tap_base, num_phases, out_scale, st, cond, take_tile_counter());
     }
     if (precision == BVG_EXACT_F32)
         return conv_simt_launch(x, w, bias, residual, accum, y_f32, y_bf16, B, T, Cin, N, cout_phase, taps, dil, tap_base,
@@ -84,7 +101,7 @@ static int convtranspose1d(int precision, const void* x, const void* w, const fl
 struct Plan {
     int64_t B, T_mel, E;  // E = max over stages of B*T_i*C_i
     size_t op_es;         // bytes per MMA-operand element
-    size_t off_mel, off_pre, off_x, off_sum, off_sumop, total;
+    size_t off_mel, off_pre, off_x, off_sum, off_sumop, off_ctr, total;
     size_t off_r[BVG_MAX_KERNELS], off_a[BVG_MAX_KERNELS], off_y1[BVG_MAX_KERNELS];  // per AMP block (they run concurrently)
 };
 
@@ -152,6 +169,7 @@ static int make_plan(const bvg_model_desc* m, int64_t B, int64_t T_mel, Plan* pl
         pl->off_a[j] = o;  o += align256((size_t)E * pl->op_es);
         pl->off_y1[j] = o; o += align256((size_t)E * y1_es);
     }
+    pl->off_ctr = o;   o += align256((size_t)BVG_MAX_TILE_COUNTERS * 2 * sizeof(unsigned int));
     pl->total = o;
     return BVG_OK;
 }
@@ -304,6 +322,14 @@ static int forward_impl(const bvg_model_desc* m, const float* mel, int mel_layou
     const int y1_dt = tc ? BVG_BF16 : BVG_F32;
     const int precise = tc ? 0 : 1;
     uint8_t* ws = static_cast<uint8_t*>(workspace);
+    // tile counters of this call's conv launches, zeroed in stream order before the first kernel (a memset node under capture)
+    TileCounterScope counter_scope;
+    static const bool dyn_env = []() { const char* e = getenv("BVG_CONV_DYNAMIC"); return e != nullptr && atoi(e) != 0; }();
+    if (dyn_env && prec != BVG_EXACT_F32) {
+        BVG_CUDA(cudaMemsetAsync(ws + pl.off_ctr, 0, (size_t)BVG_MAX_TILE_COUNTERS * 2 * sizeof(unsigned int), st));
+        t_tile_ctr.base = reinterpret_cast<unsigned int*>(ws + pl.off_ctr);
+        t_tile_ctr.next = 0;
+    }
     void* mel_nlc = ws + pl.off_mel;
     void* pre = ws + pl.off_pre;
     float* X = reinterpret_cast<float*>(ws + pl.off_x);

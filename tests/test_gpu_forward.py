@@ -346,3 +346,39 @@ def test_cfg2_full_batch_vs_oracle(full_models):
     for i in range(16):
         assert snr_db(ref32[i], got16[i]) >= 40.0, f"utterance {i} in bf16 mode"
     m.set_precision("fp32")
+
+
+def test_dynamic_tile_scheduler_opt_in_is_bit_identical(tmp_path):
+    """BVG_CONV_DYNAMIC=1 (conv CTAs take tiles from a per-launch counter in the plan's workspace instead of static
+    striding; off by default, read once per process): the mini generator's waveform in both precisions, ragged T and
+    B > 1, equals the default scheduler's bit for bit (a tile computed twice or skipped would show)."""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = f"""
+import sys
+sys.path.insert(0, {root!r}); sys.path.insert(0, {os.path.join(root, 'tests')!r})
+import numpy as np, torch
+from helpers import MINI_H, O, build_model
+sd = O.make_state_dict(MINI_H, seed=9)
+m = build_model(MINI_H, sd, precision="bf16")
+g = torch.Generator().manual_seed(2)
+out = {{}}
+for name, (B, T) in (("a", (3, 301)), ("b", (1, 64))):
+    mel = torch.randn(B, 80, T, generator=g).cuda()
+    for prec in ("bf16", "fp32"):
+        m.set_precision(prec)
+        with torch.no_grad():
+            out[name + prec] = m(mel).cpu().numpy()
+np.savez(sys.argv[1], **out)
+"""
+    files = []
+    for dyn in ("0", "1"):
+        f = str(tmp_path / f"dyn{dyn}.npz")
+        env = dict(os.environ, BVG_CONV_DYNAMIC=dyn)
+        r = subprocess.run([sys.executable, "-c", code, f], env=env, capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0, r.stderr[-3000:]
+        files.append(np.load(f))
+    for k in files[0].files:
+        assert np.isfinite(files[1][k]).all()
+        assert np.array_equal(files[0][k], files[1][k]), f"{k}: dynamic scheduler changed the result"
