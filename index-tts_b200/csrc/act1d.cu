@@ -15,7 +15,7 @@
 //    channels and each input element is loaded exactly once (plus a 6-row warm-up per time segment).  Loads and
 //    stores are coalesced across the channel axis.
 //  * act1d_ncl_kernel  -- public [B,C,T] layout.  A CTA stages a halo'd time tile of one (b,c) row in shared
-//    memory with one bulk asynchronous copy (TMA engine, cp.async.bulk + mbarrier), each thread computes 16
+//    memory with one bulk asynchronous copy (TMA engine, cp.async.bulk + mbarrier), each thread computes 24
 //    consecutive outputs from registers and writes them with 128-bit stores.
 #include "bvg_common.cuh"
 #include "sm100_ptx.cuh"
@@ -291,8 +291,16 @@ act1d_nlc_tma_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_con
 // [B,C,T] kernel with a TMA-staged halo'd time tile
 // ------------------------------------------------------------------------------------------------------------
 constexpr int NCL_THREADS = 128;
-constexpr int NCL_PER_THREAD = 16;
-constexpr int NCL_TILE = NCL_THREADS * NCL_PER_THREAD;  // 2048 outputs per CTA
+// 24 outputs per thread: 25 % halo work in the up-sampler instead of 37.5 % at 16, and a 96-byte lane stride makes the
+// 128-bit shared-memory reads 2-way instead of 4-way bank conflicted; 32 (128-byte stride: 8-way conflicts, 130 registers)
+// is 35 % slower.  cfg3, C = 1536, T = 2^21, fp32: 16 -> 0.75, 24 -> 0.81, 32 -> 0.51 of the HBM peak
+// (profiles/r02_ncl_outputs_per_thread.log).
+#ifndef BVG_NCL_PT
+#define BVG_NCL_PT 24
+#endif
+constexpr int NCL_PER_THREAD = BVG_NCL_PT;              // outputs per thread (multiple of 8)
+constexpr int NCL_XR = NCL_PER_THREAD + 16;             // per-thread input window x[i0-8 .. i0+PT+8)
+constexpr int NCL_TILE = NCL_THREADS * NCL_PER_THREAD;  // outputs per CTA
 constexpr int NCL_HALO = 8;                             // >= 6; multiple of 8 keeps interior tiles 16-byte aligned
 constexpr int NCL_SMEM_ELEMS = NCL_TILE + 2 * NCL_HALO + 16;
 
@@ -307,28 +315,28 @@ struct NclIO;
 template <>
 struct NclIO<float> {
     // xr[j] = tile[base + j], j < 32, base % 4 == 0
-    static __device__ __forceinline__ void load32(const float* tile, int base, float (&xr)[32]) {
+    static __device__ __forceinline__ void load32(const float* tile, int base, float (&xr)[NCL_XR]) {
         const float4* p = reinterpret_cast<const float4*>(tile + base);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
+        for (int j = 0; j < NCL_XR / 4; ++j) {
             float4 v = p[j];
             xr[4 * j] = v.x; xr[4 * j + 1] = v.y; xr[4 * j + 2] = v.z; xr[4 * j + 3] = v.w;
         }
     }
     static __device__ __forceinline__ float get(const float* tile, int i) { return tile[i]; }
-    static __device__ __forceinline__ void store16(float* y, const float (&o)[16]) {
+    static __device__ __forceinline__ void store16(float* y, const float (&o)[NCL_PER_THREAD]) {
         float4* p = reinterpret_cast<float4*>(y);
 #pragma unroll
-        for (int j = 0; j < 4; ++j) p[j] = make_float4(o[4 * j], o[4 * j + 1], o[4 * j + 2], o[4 * j + 3]);
+        for (int j = 0; j < NCL_PER_THREAD / 4; ++j) p[j] = make_float4(o[4 * j], o[4 * j + 1], o[4 * j + 2], o[4 * j + 3]);
     }
     static __device__ __forceinline__ void store1(float* y, float v) { *y = v; }
 };
 template <>
 struct NclIO<__nv_bfloat16> {
-    static __device__ __forceinline__ void load32(const __nv_bfloat16* tile, int base, float (&xr)[32]) {
+    static __device__ __forceinline__ void load32(const __nv_bfloat16* tile, int base, float (&xr)[NCL_XR]) {
         const uint4* p = reinterpret_cast<const uint4*>(tile + base);  // base % 8 == 0
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
+        for (int j = 0; j < NCL_XR / 8; ++j) {
             uint4 v = p[j];
             const unsigned int w[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
@@ -339,10 +347,10 @@ struct NclIO<__nv_bfloat16> {
         }
     }
     static __device__ __forceinline__ float get(const __nv_bfloat16* tile, int i) { return __bfloat162float(tile[i]); }
-    static __device__ __forceinline__ void store16(__nv_bfloat16* y, const float (&o)[16]) {
+    static __device__ __forceinline__ void store16(__nv_bfloat16* y, const float (&o)[NCL_PER_THREAD]) {
         uint4* p = reinterpret_cast<uint4*>(y);
 #pragma unroll
-        for (int j = 0; j < 2; ++j) {
+        for (int j = 0; j < NCL_PER_THREAD / 8; ++j) {
             __nv_bfloat162 h0 = __floats2bfloat162_rn(o[8 * j], o[8 * j + 1]);
             __nv_bfloat162 h1 = __floats2bfloat162_rn(o[8 * j + 2], o[8 * j + 3]);
             __nv_bfloat162 h2 = __floats2bfloat162_rn(o[8 * j + 4], o[8 * j + 5]);
@@ -356,45 +364,45 @@ struct NclIO<__nv_bfloat16> {
 
 // xr[j] = tile[base4 + D + j], j < 32, base4 % 4 == 0, 0 < D < 4 (rows that start D floats into a 16-byte vector)
 template <int D>
-__device__ __forceinline__ void ncl_load32_shifted(const float* tile, int base4, float (&xr)[32]) {
+__device__ __forceinline__ void ncl_load32_shifted(const float* tile, int base4, float (&xr)[NCL_XR]) {
     const float4* p = reinterpret_cast<const float4*>(tile + base4);
-    float buf[36];
+    float buf[NCL_XR + 4];
 #pragma unroll
-    for (int j = 0; j < 9; ++j) {
+    for (int j = 0; j < NCL_XR / 4 + 1; ++j) {
         const float4 v = p[j];
         buf[4 * j] = v.x; buf[4 * j + 1] = v.y; buf[4 * j + 2] = v.z; buf[4 * j + 3] = v.w;
     }
 #pragma unroll
-    for (int j = 0; j < 32; ++j) xr[j] = buf[j + D];
+    for (int j = 0; j < NCL_XR; ++j) xr[j] = buf[j + D];
 }
 // 16 fp32 outputs to a row address that is H floats short of a 16-byte boundary (0 < H < 4): H scalars, three aligned
 // vectors, 4 - H scalars.
 template <int H>
-__device__ __forceinline__ void ncl_store16_shifted(float* y, const float (&o)[16]) {
+__device__ __forceinline__ void ncl_store16_shifted(float* y, const float (&o)[NCL_PER_THREAD]) {
 #pragma unroll
     for (int j = 0; j < H; ++j) y[j] = o[j];
 #pragma unroll
-    for (int v = 0; v < 3; ++v)
+    for (int v = 0; v < NCL_PER_THREAD / 4 - 1; ++v)
         *reinterpret_cast<float4*>(y + H + 4 * v) = make_float4(o[H + 4 * v], o[H + 4 * v + 1], o[H + 4 * v + 2], o[H + 4 * v + 3]);
 #pragma unroll
-    for (int j = H + 12; j < 16; ++j) y[j] = o[j];
+    for (int j = H + NCL_PER_THREAD - 4; j < NCL_PER_THREAD; ++j) y[j] = o[j];
 }
 
 // out[q] = y[i0 + q], q < 16, from xr[j] = x[cl(i0 - 8 + j)].  EDGE: the thread touches an end of the row (replicate
 // padding of the activated 2x signal).
 template <bool PRECISE, bool EDGE>
-__device__ __forceinline__ void ncl_compute16(const float (&xr)[32], const SnakeCoef& coef, int64_t i0, int64_t T,
+__device__ __forceinline__ void ncl_compute16(const float (&xr)[NCL_XR], const SnakeCoef& coef, int64_t i0, int64_t T,
                                               float (&out)[NCL_PER_THREAD]) {
     const float e0 = 2.f * BVG_F0, e1 = 2.f * BVG_F1, e2 = 2.f * BVG_F2, e3 = 2.f * BVG_F3, e4 = 2.f * BVG_F4,
                 e5 = 2.f * BVG_F5;
     // The packed up-sampler reads (x[a], x[a+1]) for every a: an FFMA2 operand is an even-aligned 64-bit register pair,
     // so the odd-start pairs are materialised ONCE (30 MOVs) instead of being re-assembled at each of their six uses
     // (ncu r02y: ~250 MOVs of 880 instructions per thread, issue slots 81 % busy against 67 % for the FMA pipe).
-    float2 xe[16], xo[15];
+    float2 xe[NCL_XR / 2], xo[NCL_XR / 2 - 1];
 #pragma unroll
-    for (int i = 0; i < 16; ++i) xe[i] = make_float2(xr[2 * i], xr[2 * i + 1]);
+    for (int i = 0; i < NCL_XR / 2; ++i) xe[i] = make_float2(xr[2 * i], xr[2 * i + 1]);
 #pragma unroll
-    for (int i = 0; i < 15; ++i) xo[i] = make_float2(xr[2 * i + 1], xr[2 * i + 2]);
+    for (int i = 0; i < NCL_XR / 2 - 1; ++i) xo[i] = make_float2(xr[2 * i + 1], xr[2 * i + 2]);
 #define NCL_X2(a) (((a) & 1) ? xo[(a) >> 1] : xe[(a) >> 1])
     // v2[p] = (v[2m], v[2m+1]) for m = i0 - 3 + p
     float2 v2[NCL_PER_THREAD + 6];
@@ -475,9 +483,9 @@ act1d_ncl_kernel(const TIO* __restrict__ x, TIO* __restrict__ y, const float* __
     const bool active = i0 < T;  // no early return: every thread reaches the staging barrier below
 
     // xr[j] = x[cl(i0 - 8 + j)]
-    float xr[32];
+    float xr[NCL_XR];
     if (active) {
-        if (i0 - 8 >= lo && i0 + 24 <= hi) {  // interior thread: no clamping
+        if (i0 - 8 >= lo && i0 + NCL_PER_THREAD + 8 <= hi) {  // interior thread: no clamping
             const int base = delta + static_cast<int>(i0 - 8 - lo);
             if (delta == 0) {
                 NclIO<TIO>::load32(tile, base, xr);
@@ -492,11 +500,11 @@ act1d_ncl_kernel(const TIO* __restrict__ x, TIO* __restrict__ y, const float* __
                 }
             } else {  // bf16 row not 16-byte aligned: scalar shared-memory reads, still no index arithmetic per element
 #pragma unroll
-                for (int j = 0; j < 32; ++j) xr[j] = NclIO<TIO>::get(tile, base + j);
+                for (int j = 0; j < NCL_XR; ++j) xr[j] = NclIO<TIO>::get(tile, base + j);
             }
         } else {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
+            for (int j = 0; j < NCL_XR; ++j) {
                 int64_t idx = i0 - 8 + j;
                 idx = idx < 0 ? 0 : (idx >= T ? T - 1 : idx);
                 xr[j] = NclIO<TIO>::get(tile, delta + static_cast<int>(idx - lo));
@@ -504,7 +512,7 @@ act1d_ncl_kernel(const TIO* __restrict__ x, TIO* __restrict__ y, const float* __
         }
     } else {
 #pragma unroll
-        for (int j = 0; j < 32; ++j) xr[j] = 0.f;
+        for (int j = 0; j < NCL_XR; ++j) xr[j] = 0.f;
     }
 
     // interior threads (every activated pair m = i0-3 .. i0+18 lies inside the row) skip the replicate-padding logic of

@@ -35,10 +35,11 @@ def test_activation1d_ncl_golden_fp32(ops, golden_dir):
         np.testing.assert_allclose(y, g[f"y64_{i}"], rtol=0, atol=2e-5, err_msg=f"case {i} shape {x.shape}")
 
 
-@pytest.mark.parametrize("T", [1, 7, 2047, 2048, 2049, 4096 + 37, 50000])
+@pytest.mark.parametrize("T", [1, 7, 2047, 2048, 2049, 3071, 3072, 3073, 3080, 4096 + 37, 6144 + 24, 50000])
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
 def test_activation1d_ncl_vs_oracle(ops, T, dtype):
-    """Tile edges (2048-sample tiles, 16 outputs per thread), odd T (unaligned rows -> scalar path), both IO dtypes.
+    """Tile edges (3072-sample tiles, 24 outputs per thread; 2048 was the round-1 tile), odd T (unaligned rows -> shifted
+    vector path for fp32, staged scalar path for bf16), both IO dtypes.
     fp32/precise: max-abs <= 2e-5.  bf16 IO / MUFU: output rounding dominates: <= 2^-7 relative to max |y|."""
     rng = np.random.default_rng(T)
     B, C = 2, 6
@@ -63,7 +64,7 @@ def test_activation1d_ncl_cfg3_full_size(ops, T, dtype):
     """BASELINE.json configs[2] at full size: the public [B, C, T] op at C = 1536, T = 2^21 (aligned) and 2^20 + 37 (odd
     rows -> unaligned path).  The oracle checks the first and last 4096 samples of a few channels (the op is local: an
     output depends on x within +-6 samples, so a slice with a 64-sample margin reproduces it exactly), plus a window that
-    straddles a tile boundary in the middle; a checksum over every channel guards against rows that were never written."""
+    straddles tile boundaries in the middle; a checksum over every channel guards against rows that were never written."""
     C = 1536
     g = torch.Generator(device="cuda").manual_seed(T % 1000)
     x = (1.5 * torch.randn(1, C, T, device="cuda", generator=g)).to(dtype)
@@ -75,7 +76,7 @@ def test_activation1d_ncl_cfg3_full_size(ops, T, dtype):
     assert bool(torch.isfinite(y.float().sum(dim=2)).all())   # every row written with finite values
     chans = [0, 1, 767, 1534, 1535]
     n, margin = 4096, 64
-    mid = (T // 2 // 2048) * 2048 - n // 2   # window across a 2048-sample tile edge
+    mid = (T // 2 // 3072) * 3072 - n // 2   # window across a 3072-sample tile edge
     for lo, hi, keep_lo, keep_hi in ((0, n + margin, 0, n), (T - n - margin, T, T - n, T), (mid - margin, mid + n + margin, mid, mid + n)):
         xs = x[0, chans, lo:hi].float().cpu().numpy().astype(np.float64)[None]
         ref = O.activation1d(xs, al[chans].cpu().numpy(), be[chans].cpu().numpy())[0][:, keep_lo - lo:keep_hi - lo]
