@@ -375,6 +375,33 @@ def main():
         if r["kind"] != "layout":
             roof_ms_total += roof
             meas_ms_total += r["ms"]
+    # The same roofline with the bytes the plan's kernels really move in bf16 mode (fp32 residual stream):
+    # SURVEY.md 8(d) charges 2 bytes per element everywhere, but the second conv of every AMP sub-block reads an fp32
+    # residual and writes an fp32 result (bf16 operand 2 + 4 + 4 bytes per output element), and the first activation of a
+    # sub-block reads the fp32 residual stream (4 + 2 bytes).  Layers are recognised from the record sequence.
+    roof_actual_ms = 0.0
+    if args.precision == "bf16":
+        for i, r in enumerate(recs):
+            if r["kind"] == "layout":
+                continue
+            rows, cin, cout, k = float(r["rows"]), float(r["cin"]), float(r["cout"]), float(max(r["k"], 1))
+            b_act = r["bytes"]
+            if r["kind"] == "conv1d" and r["stage"] >= 0:
+                plain = 2.0 * rows * (cin + cout) + 2.0 * cin * cout * k + 4.0 * cout
+                if r["bytes"] > plain * 1.05:  # carries the residual term: fp32 residual in, fp32 out
+                    b_act = 2.0 * rows * cin + 8.0 * rows * cout + 2.0 * cin * cout * k + 4.0 * cout
+            elif r["kind"] == "activation1d":
+                heads = max(1, int(round(r["flops"] / (62.0 * rows * cin))))
+                nxt = recs[i + 1] if i + 1 < len(recs) else None
+                if r["stage"] < 0:
+                    b_act = 8.0 * rows * cin                       # activation_post: fp32 in, fp32 out
+                elif heads > 1:
+                    b_act = (4.0 + 2.0 * heads) * rows * cin       # shared up-sampler: one fp32 read, `heads` bf16 outputs
+                elif nxt is not None and nxt["kind"] == "conv1d" and nxt["bytes"] <= (2.0 * rows * 2 * cin + 2.0 * cin * cin * max(nxt["k"], 1) + 4.0 * cin) * 1.05:
+                    b_act = 6.0 * rows * cin                       # first activation of a sub-block: fp32 residual stream in
+            elif r["kind"] == "convtranspose1d":
+                b_act = r["bytes"] + 2.0 * rows * cout             # the up-sampled residual stream is written as fp32 (4 B, not 2)
+            roof_actual_ms += max(r["flops"] / (peaks["tf_sus"] * 1e12), b_act / (peaks["hbm"] * 1e9)) * 1e3
     conv = by.get("conv1d", {"ms": 1.0, "flops": 0.0, "n": 0})
     convt = by.get("convtranspose1d", {"ms": 0.0, "flops": 0.0, "n": 0})
     mma_ms = conv["ms"] + convt["ms"]
@@ -586,7 +613,10 @@ def main():
         "roofline": roofline,
         "per_layer_roofline": {"roofline_ms": roof_ms_total, "measured_ms": meas_ms_total,
                                "frac": roof_ms_total / meas_ms_total if meas_ms_total > 0 else None,
-                               "definition": "sum over layers of max(FLOPs/bf16 sustained peak, algorithmic bytes/HBM peak) / sum of CUDA-event kernel times"},
+                               "definition": "sum over layers of max(FLOPs/bf16 sustained peak, algorithmic bytes/HBM peak) / sum of CUDA-event kernel times",
+                               "roofline_ms_actual_traffic": roof_actual_ms if roof_actual_ms > 0 else None,
+                               "frac_actual_traffic": (roof_actual_ms / meas_ms_total) if (roof_actual_ms > 0 and meas_ms_total > 0) else None,
+                               "actual_traffic_note": "same sum with the bytes the bf16-mode plan really moves (fp32 residual stream: 10 B per element for the second conv of a sub-block, 6 B for its first activation) instead of SURVEY.md 8(d)'s 2 B per element"},
         "kernels": kernels,
         "long_form": long_form,
         "v1_generator": v1_line,
