@@ -101,3 +101,26 @@ def test_infer_v2_vocoder_tail_unchanged():
         assert fused.dtype == torch.int16 and torch.equal(fused, pcm)
     finally:
         dropin.uninstall()
+
+
+@pytest.mark.slow
+def test_bench_reference_arm_prints_one_contract_line():
+    """`bench.py --impl reference` (the driver's CPU arm) needs no GPU: exactly one JSON line on stdout with the contract's
+    keys, the CPU implementation named in `cpu_baseline.kind` and the bounded sample it really ran."""
+    import json
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, BVG_REF_BUDGET_S="4")  # halves the sample down to ~108 frames: seconds instead of minutes
+    r = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0"],
+                       capture_output=True, text=True, timeout=900, env=env, cwd=root)
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = [l for l in r.stdout.splitlines() if l.strip()]
+    assert len(lines) == 1, r.stdout[-1000:]
+    j = json.loads(lines[0])
+    for key in ("impl", "metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "config",
+                "cpu_baseline", "e2e"):
+        assert key in j, key
+    assert j["impl"] == "reference" and j["unit"] == "audio-s/s" and j["value"] > 0
+    assert j["cpu_baseline"]["kind"] in ("reference", "port") and j["cpu_baseline"]["cores"] >= 1
+    assert j["e2e"]["h2d_bytes_per_step"] == 0 and j["e2e"]["d2h_bytes_per_step"] == 0
